@@ -1,0 +1,180 @@
+/*
+ * vs_tracker.h — C ABI of the B200-native VINS-Mono visual front-end.
+ *
+ * Drop-in boundary for the hot path of chansoopark98/Mobile-SLAM:
+ *     frontend::FeatureTracker            include/frontend/feature_tracker.h:25-76
+ *     FeatureTracker::detectAndTrack      src/frontend/feature_tracker.cpp:97-201
+ * The reference has no FFI of its own (its boundary is that C++ class, read through public
+ * members by src/utility/measurement_processor.cpp:191-231 and src/vio_engine.cpp:210-239), so
+ * the entry points below are what a header-compatible adapter class binds — see
+ * include/vs_feature_tracker.hpp (C++ adapter) and INTEGRATION.md (reference-side stub).
+ *
+ * Plain C: pointers and sizes only, no OpenCV / Eigen / STL / torch types.
+ * All functions return 0 on success or a negative vs_status; vs_last_error() gives the text.
+ * Calls on one handle must be serialised by the caller (same rule as the reference class).
+ * There is NO CPU fallback: every entry point that computes runs CUDA kernels on the
+ * handle's device and fails with VS_ERR_CUDA if that is impossible.
+ */
+#ifndef VS_TRACKER_H_
+#define VS_TRACKER_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VS_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define VS_API __attribute__((visibility("default")))
+#else
+#define VS_API
+#endif
+
+typedef enum vs_status {
+    VS_OK = 0,
+    VS_ERR_INVALID = -1,   /* bad argument / config           */
+    VS_ERR_CUDA = -2,      /* CUDA runtime failure            */
+    VS_ERR_NOMEM = -3,     /* host or device allocation       */
+    VS_ERR_CAPACITY = -4,  /* max_cnt above handle capacity   */
+    VS_ERR_STATE = -5      /* call not valid in this state    */
+} vs_status;
+
+/* common::camera_models::Camera::ModelType, include/common/camera_models/Camera.h:15 */
+typedef enum vs_camera_model {
+    VS_CAM_KANNALA_BRANDT = 0,
+    VS_CAM_MEI = 1,
+    VS_CAM_PINHOLE = 2,
+    VS_CAM_SCARAMUZZA = 3
+} vs_camera_model;
+
+/* Replaces FeatureTracker::readIntrinsicParameter / setIntrinsicParameter
+ * (feature_tracker.cpp:318-336) and the m_camera object they build. */
+typedef struct vs_camera {
+    int32_t model_type;     /* vs_camera_model */
+    int32_t width, height;
+    double fx, fy, cx, cy;  /* pinhole fx..cy | KB mu,mv,u0,v0 | MEI gamma1,gamma2,u0,v0 | OCAM -, -, center_x, center_y */
+    double d[4];            /* pinhole/MEI: k1,k2,p1,p2 | KB: k2,k3,k4,k5 */
+    double xi;              /* MEI mirror parameter */
+    double poly[5];         /* SCARAMUZZA forward polynomial (SCARAMUZZA_POLY_SIZE = 5) */
+    double aff_c, aff_d, aff_e; /* SCARAMUZZA affine C, D, E */
+} vs_camera;
+
+/* Replaces the fields of the global utility::g_config the tracker reads on every call
+ * (include/utility/config.h:18-56), captured per handle instead of per process. */
+typedef struct vs_tracker_config {
+    int32_t struct_size;    /* = sizeof(vs_tracker_config) */
+    int32_t device;         /* CUDA device ordinal */
+    int32_t n_streams;      /* independent camera streams tracked by this handle (>=1) */
+    int32_t width, height;  /* g_config.camera.col / row */
+    double focal_length;    /* g_config.camera.focal_length (virtual pinhole for F-matrix RANSAC) */
+    int32_t max_cnt;        /* feature_tracker.max_cnt  (150) */
+    int32_t min_dist;       /* feature_tracker.min_dist (30)  */
+    double f_threshold;     /* feature_tracker.f_threshold (1.0) */
+    double f_threshold_edge_factor; /* (0 = off) */
+    int32_t equalize;       /* CLAHE(3.0, 8x8) on/off (1) */
+    int32_t fisheye;        /* circular/auto fisheye mask on/off (0) */
+    int32_t lk_window_size;     /* 21 */
+    int32_t lk_pyramid_levels;  /* = OpenCV maxLevel: levels 0..N (3) */
+    int32_t lk_iterations;      /* 30 */
+    double lk_eps;              /* 0.01 */
+    int32_t fb_check;       /* 0 = reference semantics (forward LK only); 1 = add backward consistency check */
+    double fb_threshold;    /* px, used when fb_check */
+    int32_t ransac_mode;    /* vs_ransac_mode */
+    int32_t capacity;       /* max features per stream the handle can ever hold (0 = max(max_cnt, 256)) */
+    const uint8_t* fisheye_mask_image; /* optional H x W mask (255 = keep), replaces the auto circle; may be NULL */
+    int32_t fisheye_mask_stride;
+    int32_t first_feature_id;   /* initial value of the per-stream n_id counter (0) */
+    vs_camera camera;
+} vs_tracker_config;
+
+typedef enum vs_ransac_mode {
+    VS_RANSAC_OFF = 0,      /* skip rejectWithFundamentalMatrix (stage isolation / latency mode) */
+    VS_RANSAC_DEVICE = 1,   /* built-in 7-point RANSAC evaluated on the GPU */
+    VS_RANSAC_CALLBACK = 2  /* host callback (e.g. cv::findFundamentalMat in the adapter) */
+} vs_ransac_mode;
+
+/* Host-side outlier rejection hook (feature_tracker.cpp:203-307).  Points are the float32
+ * virtual-pinhole coordinates the reference hands to cv::findFundamentalMat; next_px are the raw
+ * pixel positions (for the edge-recovery rule).  Fill status[i] in {0,1}. Return 0 on success. */
+typedef int (*vs_reject_fn)(void* user, int32_t stream, int32_t n, const float* un_cur_xy,
+                            const float* un_next_xy, const float* next_px_xy, uint8_t* status);
+
+/* Per-stream view of the tracker's public vectors after a frame
+ * (cur_pts, cur_undistorted_pts, pts_velocity, ids, track_cnt — feature_tracker.h:53-57).
+ * Pointers reference pinned host memory owned by the handle, valid until the next track call. */
+typedef struct vs_track_result {
+    int32_t n;                /* number of features, all index-aligned below */
+    int32_t n_new;            /* the last n_new entries were detected this frame (reference: ids == -1 until updateID) */
+    const int32_t* ids;
+    const int32_t* track_cnt;
+    const float* cur_pts;     /* n x 2, distorted pixel coordinates */
+    const float* undist;      /* n x 2, liftProjective x/z, y/z */
+    const float* velocity;    /* n x 2 */
+    /* per-frame counters */
+    int32_t n_lk_in, n_lk_ok, n_ransac_in, n_ransac_out, n_mask_kept, n_candidates;
+    int32_t ransac_ran;
+    float rms_disp;
+} vs_track_result;
+
+VS_API const char* vs_last_error(void);
+VS_API int vs_abi_version(void);
+
+/* FeatureTracker() + readIntrinsicParameter/setIntrinsicParameter */
+VS_API int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective_or_null, struct vs_tracker** out);
+VS_API void vs_tracker_destroy(struct vs_tracker* t);
+VS_API void vs_tracker_default_config(vs_tracker_config* cfg);
+
+/* detectAndTrack(img, t) + the caller's updateID loop, one stream (n_streams must be 1). */
+VS_API int vs_tracker_track(struct vs_tracker* t, const uint8_t* gray, int32_t stride, double time_s,
+                     vs_track_result* out);
+/* One frame for each of the handle's streams; frames[s] is an H x stride host image. */
+VS_API int vs_tracker_track_batch(struct vs_tracker* t, const uint8_t* const* frames, int32_t stride,
+                           const double* time_s, vs_track_result* out /* [n_streams] */);
+/* Same, frames already resident in device memory: n_streams images, each H rows of `stride` bytes,
+ * `image_stride_bytes` apart.  results_to_host = 0 leaves results on the device (fetch later). */
+VS_API int vs_tracker_track_batch_device(struct vs_tracker* t, const uint8_t* d_frames, int32_t stride,
+                                  int64_t image_stride_bytes, const double* time_s,
+                                  int32_t results_to_host, vs_track_result* out_or_null);
+VS_API int vs_tracker_fetch_results(struct vs_tracker* t, vs_track_result* out /* [n_streams] */);
+
+/* Runtime mutators, VIOEngine::setMobileParams/setFThreshold/setTrackingParams (vio_engine.cpp:354-389).
+ * Negative / zero values leave a field unchanged, exactly like the reference's guards. */
+VS_API int vs_tracker_set_params(struct vs_tracker* t, int32_t max_cnt, int32_t min_dist, double f_threshold,
+                          int32_t lk_window, int32_t lk_pyramid, int32_t lk_iterations, double lk_eps,
+                          double f_edge_factor);
+VS_API int vs_tracker_set_reject_callback(struct vs_tracker* t, vs_reject_fn fn, void* user);
+VS_API int vs_tracker_reset(struct vs_tracker* t, int32_t stream /* -1 = all */);
+/* number of CUDA kernels this handle has launched so far (bench.py "gpu_launches") */
+VS_API int64_t vs_tracker_launch_count(const struct vs_tracker* t);
+/* CUDA-event time (ms) of the device work of the last track call */
+VS_API float vs_tracker_last_device_ms(const struct vs_tracker* t);
+
+/* ---- stage entry points (same kernels as the frame path, for teacher-forced parity tests and
+ *      per-kernel roofline timing).  All buffers are host memory, images are tightly packed. ---- */
+VS_API int vs_stage_clahe(struct vs_tracker* t, const uint8_t* img, uint8_t* out);
+/* levels written back to back, tightly packed; sizes[2*l], sizes[2*l+1] = width, height */
+VS_API int vs_stage_pyramid(struct vs_tracker* t, const uint8_t* level0, uint8_t* out_levels, int32_t* sizes,
+                     int32_t* n_levels);
+VS_API int vs_stage_lk(struct vs_tracker* t, const uint8_t* prev_level0, const uint8_t* next_level0,
+                const float* pts_xy, int32_t n, float* next_xy, uint8_t* status /* raw LK status */);
+VS_API int vs_stage_min_eig(struct vs_tracker* t, const uint8_t* img, float* eig);
+/* mask = base (fisheye/all) minus min_dist discs around kept_xy; returns corners in acceptance order */
+VS_API int vs_stage_good_features(struct vs_tracker* t, const uint8_t* img, const float* kept_xy, int32_t n_kept,
+                           int32_t max_corners, float* corners_xy, int32_t* n_out, uint8_t* mask_out_or_null);
+VS_API int vs_stage_undistort(struct vs_tracker* t, const float* pts_xy, int32_t n, float* out_xy);
+/* setMask order + greedy keep (feature_tracker.cpp:62-86): keep_idx = indices into the input, in kept order */
+VS_API int vs_stage_set_mask(struct vs_tracker* t, const float* pts_xy, const int32_t* track_cnt, int32_t n,
+                      int32_t* keep_idx, int32_t* n_keep);
+/* F-matrix RANSAC on virtual-pinhole points (device implementation) */
+VS_API int vs_stage_ransac(struct vs_tracker* t, const float* a_xy, const float* b_xy, int32_t n, uint8_t* status);
+/* repeat one dense stage `reps` times on device-resident synthetic data of all streams and return
+ * the mean kernel time in ms (CUDA events); used by bench.py for per-kernel roofline numbers.
+ * stage: 0 clahe_hist 1 clahe_apply 2 pyr_down(all levels) 3 lk 4 eig_max 5 eig_candidates */
+VS_API int vs_stage_time(struct vs_tracker* t, int32_t stage, int32_t reps, float* ms_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VS_TRACKER_H_ */

@@ -1,0 +1,418 @@
+// K10 / K8 / K7 / K11 — the per-stream glue of FeatureTracker::detectAndTrack on the device.
+//   post_lk_kernel       status & inBorder filter + 6-array compaction, track_cnt++, RMS-displacement
+//                        gate, virtual-pinhole lift for the F-matrix RANSAC   (feature_tracker.cpp:138-173, 211-225)
+//   set_mask_kernel      RANSAC-status compaction, std::sort order, greedy keep with min_dist discs
+//                        (feature_tracker.cpp:62-86, 300-305)
+//   fill/paint_mask      the mask image goodFeaturesToTrack receives          (feature_tracker.cpp:40-60, 84)
+//   select_finish_kernel candidate sort + greedy min-distance selection (second half of
+//                        cv::goodFeaturesToTrack), addPoints, updateID, undistortedPoints + velocity
+//                        (feature_tracker.cpp:89-95, 309-316, 338-380)
+#include "camera.cuh"
+#include "glue.cuh"
+#include "introsort.cuh"
+
+namespace vs {
+
+__device__ __forceinline__ bool in_border(float2 p, int W, int H) {
+    const int x = cv_round(p.x), y = cv_round(p.y);
+    return 1 <= x && x < W - 1 && 1 <= y && y < H - 1;
+}
+
+// ordered block compaction helper: returns this thread's output slot (or -1) and advances *base
+__device__ __forceinline__ int block_compact_slot(bool ok, int tid, int* s_warp_cnt, int& base) {
+    const unsigned int bal = __ballot_sync(0xffffffffu, ok);
+    const int lane = tid & 31, warp = tid >> 5;
+    if (lane == 0) s_warp_cnt[warp] = __popc(bal);
+    __syncthreads();
+    int off = base, total = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = s_warp_cnt[k];
+        if (k < warp) off += c;
+        total += c;
+    }
+    __syncthreads();
+    const int slot = ok ? off + __popc(bal & ((1u << lane) - 1u)) : -1;
+    base += total;
+    return slot;
+}
+
+__global__ void __launch_bounds__(256) post_lk_kernel(GlueParams g) {
+    __shared__ int s_warp_cnt[8];
+    __shared__ double s_red[8];
+    __shared__ int s_flag;
+    const int s = blockIdx.x, tid = threadIdx.x;
+    const int64_t o = (int64_t)s * g.cap;
+    const int n = g.n[s];
+    int base = 0;
+    double acc = 0.0;
+    for (int chunk = 0; chunk < n; chunk += 256) {
+        const int i = chunk + tid;
+        bool ok = false;
+        float2 nx = make_float2(0.f, 0.f), cur = nx;
+        if (i < n) {
+            nx = g.lk_next[o + i];
+            cur = g.pts[o + i];
+            ok = g.lk_status[o + i] && in_border(nx, g.W, g.H);
+            if (ok && g.fb_check) {
+                const float2 b = g.lk_back[o + i];
+                const float dx = b.x - cur.x, dy = b.y - cur.y;
+                ok = g.lk_back_status[o + i] && (dx * dx + dy * dy <= g.fb_threshold * g.fb_threshold);
+            }
+        }
+        const int slot = block_compact_slot(ok, tid, s_warp_cnt, base);
+        if (slot >= 0) {
+            g.w_cur[o + slot] = cur;
+            g.w_next[o + slot] = nx;
+            g.w_ids[o + slot] = g.ids[o + i];
+            g.w_cnt[o + slot] = g.cnt[o + i] + 1;
+            g.w_un[o + slot] = g.un[o + i];
+            g.w_rstatus[o + slot] = 1;
+            const double dx = (double)nx.x - (double)cur.x, dy = (double)nx.y - (double)cur.y;
+            acc += dx * dx + dy * dy;
+        }
+    }
+    const int wn = base;
+#pragma unroll
+    for (int k = 16; k > 0; k >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, k);
+    if ((tid & 31) == 0) s_red[tid >> 5] = acc;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+        for (int k = 0; k < 8; ++k) t += s_red[k];
+        const double rms = wn > 0 ? sqrt(t / (double)wn) : 0.0;
+        bool should_reject = true;
+        if (wn > 0 && rms < 2.0) should_reject = false;
+        const int flag = (g.ransac_enabled && should_reject && wn >= 30) ? 1 : 0;
+        s_flag = flag;
+        g.wn[s] = wn;
+        g.ransac_flag[s] = flag;
+        int* h = g.r_hdr + (int64_t)s * kHdrInts;
+        h[H_LK_IN] = n;
+        h[H_LK_OK] = wn;
+        h[H_RANSAC_RAN] = flag;
+        h[H_RANSAC_IN] = wn;
+        h[H_RMS_BITS] = __float_as_int((float)rms);
+    }
+    __syncthreads();
+    if (s_flag) {
+        const double cx = (double)g.W / 2.0, cy = (double)g.H / 2.0;
+        for (int i = tid; i < 2 * wn; i += 256) {
+            const int j = i >> 1;
+            const float2 p = (i & 1) ? g.w_next[o + j] : g.w_cur[o + j];
+            double X, Y, Z;
+            lift_projective(g.cam, (double)p.x, (double)p.y, X, Y, Z);
+            const float2 r = make_float2((float)(g.focal_length * X / Z + cx), (float)(g.focal_length * Y / Z + cy));
+            if (i & 1) g.w_lnext[o + j] = r; else g.w_lcur[o + j] = r;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// setMask: order by track_cnt (exact libstdc++ std::sort moves), greedy keep outside painted discs
+// ---------------------------------------------------------------------------------------------
+int set_mask_smem_bytes(int cap) { return cap * (4 + 4 + 4 + 4 + 4); }
+
+__global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
+    extern __shared__ __align__(16) uint8_t dsm[];
+    int* src = reinterpret_cast<int*>(dsm);          // surviving work indices (order preserved)
+    int* key = src + g.cap;                          // track_cnt of src[j]
+    int* perm = key + g.cap;                         // sorted order (indices into src)
+    int* kidx = perm + g.cap;                        // kept work indices
+    short2* acc = reinterpret_cast<short2*>(kidx + g.cap);   // kept rounded centres
+    __shared__ int s_warp_cnt[8];
+    __shared__ int s_kn;
+    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const int64_t o = (int64_t)s * g.cap;
+    const int wn = g.wn[s];
+    const bool filt = g.ransac_flag[s] != 0;
+    int n2 = 0;
+    for (int chunk = 0; chunk < wn; chunk += 256) {
+        const int i = chunk + tid;
+        const bool ok = i < wn && (!filt || g.w_rstatus[o + i]);
+        const int slot = block_compact_slot(ok, tid, s_warp_cnt, n2);
+        if (slot >= 0) {
+            src[slot] = i;
+            key[slot] = g.w_cnt[o + i];
+            perm[slot] = slot;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) std_sort_indices(perm, n2, DescByKey{key});
+    __syncthreads();
+    if (tid < 32) {
+        const int R = g.min_dist;
+        int A = 0;
+        for (int q0 = 0; q0 < n2; q0 += 32) {
+            const int q = q0 + lane;
+            bool alive = false;
+            int rx = 0, ry = 0, widx = -1;
+            if (q < n2) {
+                widx = src[perm[q]];
+                const float2 p = g.w_next[o + widx];
+                rx = cv_round(p.x);
+                ry = cv_round(p.y);
+                alive = g.base_mask[(int64_t)ry * g.mask_pitch + rx] == 255;
+                for (int a = 0; a < A && alive; ++a) {
+                    const int dy = abs(ry - (int)acc[a].y), dx = abs(rx - (int)acc[a].x);
+                    if (dy <= R && dx <= g.disc_hw[dy]) alive = false;
+                }
+            }
+            unsigned int m = __ballot_sync(0xffffffffu, alive);
+            while (m) {
+                const int l = __ffs(m) - 1;
+                const int ax = __shfl_sync(0xffffffffu, rx, l), ay = __shfl_sync(0xffffffffu, ry, l);
+                if (lane == l) {
+                    acc[A] = make_short2((short)rx, (short)ry);
+                    kidx[A] = widx;
+                    alive = false;
+                } else if (alive && lane > l) {
+                    const int dy = abs(ry - ay), dx = abs(rx - ax);
+                    if (dy <= R && dx <= g.disc_hw[dy]) alive = false;
+                }
+                ++A;
+                m = __ballot_sync(0xffffffffu, alive);
+            }
+            __syncwarp();
+        }
+        if (lane == 0) s_kn = A;
+    }
+    __syncthreads();
+    const int kn = s_kn;
+    for (int j = tid; j < kn; j += 256) {
+        const int i = kidx[j];
+        g.k_pts[o + j] = g.w_next[o + i];
+        g.k_ids[o + j] = g.w_ids[o + i];
+        g.k_cnt[o + j] = g.w_cnt[o + i];
+        g.k_un[o + j] = g.w_un[o + i];
+    }
+    if (tid == 0) {
+        g.kn[s] = kn;
+        const int want = g.max_cnt - kn;
+        g.want[s] = want;
+        g.cand_count[s] = 0;
+        g.max_enc[s] = 0;
+        int* h = g.r_hdr + (int64_t)s * kHdrInts;
+        h[H_RANSAC_OUT] = n2;
+        h[H_MASK_KEPT] = kn;
+        h[H_WANT] = want;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// mask image: base (fisheye disc / file mask / 255) minus a filled circle of radius min_dist per kept point
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) fill_mask_kernel(GlueParams g) {
+    const int s = blockIdx.y;
+    if (g.want[s] <= 0) return;
+    const int64_t n16 = ((int64_t)g.H * g.mask_pitch) >> 4;
+    const uint4* b = reinterpret_cast<const uint4*>(g.base_mask);
+    uint4* m = reinterpret_cast<uint4*>(g.mask + (int64_t)s * g.mask_stride);
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (int64_t)gridDim.x * 256) m[i] = b[i];
+}
+
+__global__ void __launch_bounds__(64) paint_mask_kernel(GlueParams g) {
+    const int s = blockIdx.y, j = blockIdx.x;
+    if (g.want[s] <= 0 || j >= g.kn[s]) return;
+    const float2 p = g.k_pts[(int64_t)s * g.cap + j];
+    const int cx = cv_round(p.x), cy = cv_round(p.y), R = g.min_dist, D = 2 * R + 1;
+    uint8_t* m = g.mask + (int64_t)s * g.mask_stride;
+    for (int idx = threadIdx.x; idx < D * D; idx += 64) {
+        const int ry = idx / D, rx = idx - ry * D;
+        const int dy = ry - R, dx = rx - R;
+        const int y = cy + dy, x = cx + dx;
+        if (y >= 0 && y < g.H && x >= 0 && x < g.W && abs(dx) <= g.disc_hw[abs(dy)]) m[(int64_t)y * g.mask_pitch + x] = 0;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K7: sort candidates (eig desc, address desc), greedy min-distance accept, then finish the frame
+// ---------------------------------------------------------------------------------------------
+constexpr int kSortSmemKeys = 8192;
+constexpr int kFinishThreads = 1024;
+
+__device__ __forceinline__ void bitonic_sort_desc(unsigned long long* v, int N, int tid, int nthreads) {
+    for (int k = 2; k <= N; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (N >> 1); t += nthreads) {
+                const int i = 2 * j * (t / j) + (t % j);
+                const int l = i + j;
+                const unsigned long long a = v[i], b = v[l];
+                const bool desc = (i & k) == 0;
+                if ((a < b) == desc) {
+                    v[i] = b;
+                    v[l] = a;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kFinishThreads) select_finish_kernel(GlueParams g) {
+    extern __shared__ __align__(16) uint8_t dsm[];
+    unsigned long long* skeys = reinterpret_cast<unsigned long long*>(dsm);       // [kSortSmemKeys]
+    short2* newp = reinterpret_cast<short2*>(skeys + kSortSmemKeys);               // [cap]
+    __shared__ int s_nnew;
+    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const int64_t o = (int64_t)s * g.cap;
+    const int kn = g.kn[s];
+    int want = g.want[s];
+    if (want > g.cap - kn) want = g.cap - kn;
+    if (tid == 0) s_nnew = 0;
+    int nc = 0;
+    if (want > 0) {
+        nc = g.cand_count[s];
+        if (nc > g.cand_cap) nc = g.cand_cap;
+    }
+    __syncthreads();
+    if (nc > 0) {
+        int N = 1;
+        while (N < nc) N <<= 1;
+        unsigned long long* gk = g.cand + (int64_t)s * g.cand_cap;
+        unsigned long long* v;
+        if (N <= kSortSmemKeys) {
+            for (int i = tid; i < N; i += kFinishThreads) skeys[i] = i < nc ? gk[i] : 0ull;
+            v = skeys;
+        } else {
+            for (int i = nc + tid; i < N; i += kFinishThreads) gk[i] = 0ull;
+            v = gk;
+        }
+        __syncthreads();
+        bitonic_sort_desc(v, N, tid, kFinishThreads);
+        if (tid < 32) {
+            const int W = g.W;
+            const int md2 = g.min_dist * g.min_dist;
+            int A = 0;
+            for (int q0 = 0; q0 < nc && A < want; q0 += 32) {
+                const int q = q0 + lane;
+                bool alive = q < nc;
+                int x = 0, y = 0;
+                if (alive) {
+                    const unsigned int lin = (unsigned int)(v[q] & 0xffffffffull);
+                    y = lin / W;
+                    x = lin - y * W;
+                    for (int a = 0; a < A && alive; ++a) {
+                        const int dx = x - (int)newp[a].x, dy = y - (int)newp[a].y;
+                        if (dx * dx + dy * dy < md2) alive = false;
+                    }
+                }
+                unsigned int m = __ballot_sync(0xffffffffu, alive);
+                while (m && A < want) {
+                    const int l = __ffs(m) - 1;
+                    const int ax = __shfl_sync(0xffffffffu, x, l), ay = __shfl_sync(0xffffffffu, y, l);
+                    if (lane == l) {
+                        newp[A] = make_short2((short)x, (short)y);
+                        alive = false;
+                    } else if (alive && lane > l) {
+                        const int dx = x - ax, dy = y - ay;
+                        if (dx * dx + dy * dy < md2) alive = false;
+                    }
+                    ++A;
+                    m = __ballot_sync(0xffffffffu, alive);
+                }
+                __syncwarp();
+            }
+            if (lane == 0) s_nnew = A;
+        }
+    }
+    __syncthreads();
+    const int n_new = s_nnew;
+    const int total = kn + n_new;
+    const int id0 = g.next_id[s];
+    const double t_cur = g.cur_time[s];
+    const double dt = t_cur - g.prev_time[s];
+    for (int i = tid; i < total; i += kFinishThreads) {
+        float2 p, un_prev = make_float2(0.f, 0.f);
+        int id, c;
+        if (i < kn) {
+            p = g.k_pts[o + i];
+            id = g.k_ids[o + i];
+            c = g.k_cnt[o + i];
+            un_prev = g.k_un[o + i];
+        } else {
+            p = make_float2((float)newp[i - kn].x, (float)newp[i - kn].y);
+            id = id0 + (i - kn);
+            c = 1;
+        }
+        double X, Y, Z;
+        lift_projective(g.cam, (double)p.x, (double)p.y, X, Y, Z);
+        const float2 un = make_float2((float)(X / Z), (float)(Y / Z));
+        // velocity: only features whose id was already assigned when the previous frame's map was
+        // built (track_cnt >= 3 now) are found in prev_undistorted_pts_map (feature_tracker.cpp:351-378)
+        float2 vel = make_float2(0.f, 0.f);
+        if (i < kn && c >= 3 && dt > 1e-4) {
+            vel.x = (float)((double)__fsub_rn(un.x, un_prev.x) / dt);
+            vel.y = (float)((double)__fsub_rn(un.y, un_prev.y) / dt);
+        }
+        g.pts[o + i] = p;
+        g.ids[o + i] = id;
+        g.cnt[o + i] = c;
+        g.un[o + i] = un;
+        g.r_pts[o + i] = p;
+        g.r_ids[o + i] = id;
+        g.r_cnt[o + i] = c;
+        g.r_un[o + i] = un;
+        g.r_vel[o + i] = vel;
+    }
+    if (tid == 0) {
+        g.n[s] = total;
+        g.next_id[s] = id0 + n_new;
+        g.prev_time[s] = t_cur;
+        int* h = g.r_hdr + (int64_t)s * kHdrInts;
+        h[H_N] = total;
+        h[H_NNEW] = n_new;
+        h[H_NCAND] = nc;
+    }
+}
+
+__global__ void undistort_kernel(CameraDev cam, const float2* __restrict__ pts, int n, float2* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double X, Y, Z;
+    lift_projective(cam, (double)pts[i].x, (double)pts[i].y, X, Y, Z);
+    out[i] = make_float2((float)(X / Z), (float)(Y / Z));
+}
+
+void launch_post_lk(const GlueParams& g, cudaStream_t st, int64_t* launches) {
+    post_lk_kernel<<<g.n_streams, 256, 0, st>>>(g);
+    if (launches) *launches += 1;
+}
+
+void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches) {
+    const int smem = set_mask_smem_bytes(g.cap);
+    static int configured = 0;
+    if (smem > 48 * 1024 && configured < smem) {
+        cudaFuncSetAttribute(set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured = smem;
+    }
+    set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
+    if (launches) *launches += 1;
+}
+
+void launch_paint_mask(const GlueParams& g, cudaStream_t st, int64_t* launches) {
+    const int64_t n16 = ((int64_t)g.H * g.mask_pitch) >> 4;
+    int blocks = (int)((n16 + 255) / 256);
+    if (blocks > 64) blocks = 64;
+    fill_mask_kernel<<<dim3(blocks, g.n_streams), 256, 0, st>>>(g);
+    paint_mask_kernel<<<dim3(g.max_cnt, g.n_streams), 64, 0, st>>>(g);
+    if (launches) *launches += 2;
+}
+
+void launch_select_finish(const GlueParams& g, cudaStream_t st, int64_t* launches) {
+    const int smem = kSortSmemKeys * 8 + g.cap * 4;
+    static int configured = 0;
+    if (configured < smem) {
+        cudaFuncSetAttribute(select_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured = smem;
+    }
+    select_finish_kernel<<<g.n_streams, kFinishThreads, smem, st>>>(g);
+    if (launches) *launches += 1;
+}
+
+void launch_undistort(const CameraDev& cam, const float2* pts, int n, float2* out, cudaStream_t st) {
+    if (n <= 0) return;
+    undistort_kernel<<<(n + 127) / 128, 128, 0, st>>>(cam, pts, n, out);
+}
+
+}  // namespace vs

@@ -1,0 +1,170 @@
+// libstdc++ std::sort, restated so the reference's UNSTABLE tie order can be reproduced on the device.
+//
+// FeatureTracker::setMask sorts (track_cnt, point, id) triples with std::sort and a comparator that
+// looks at track_cnt only (/root/reference/src/frontend/feature_tracker.cpp:70-73); which of two
+// equally old features survives the min-distance greedy therefore depends on the exact element moves
+// of GCC's introsort (bits/stl_algo.h: __introsort_loop, threshold 16, median-of-3 to first,
+// __unguarded_partition, heap-sort fallback at depth 2*floor(log2 n), __final_insertion_sort).
+// This header re-implements that algorithm step for step on an index array `v` with keys `key[v[i]]`;
+// tests/test_host_logic.py checks it against the real std::sort (oracle/stdsort.cpp) on tie-heavy input.
+#pragma once
+#ifndef __CUDACC__
+#ifndef __host__
+#define __host__
+#define __device__
+#endif
+#endif
+
+namespace vs {
+
+struct DescByKey {
+    const int* key;
+    __host__ __device__ bool operator()(int a, int b) const { return key[a] > key[b]; }
+};
+
+template <class Comp>
+__host__ __device__ inline void iso_swap(int* v, int a, int b, Comp) {
+    const int t = v[a];
+    v[a] = v[b];
+    v[b] = t;
+}
+
+template <class Comp>
+__host__ __device__ inline void iso_push_heap(int* v, int first, int hole, int top, int value, Comp comp) {
+    int parent = (hole - 1) / 2;
+    while (hole > top && comp(v[first + parent], value)) {
+        v[first + hole] = v[first + parent];
+        hole = parent;
+        parent = (hole - 1) / 2;
+    }
+    v[first + hole] = value;
+}
+
+template <class Comp>
+__host__ __device__ inline void iso_adjust_heap(int* v, int first, int hole, int len, int value, Comp comp) {
+    const int top = hole;
+    int child = hole;
+    while (child < (len - 1) / 2) {
+        child = 2 * (child + 1);
+        if (comp(v[first + child], v[first + child - 1])) child--;
+        v[first + hole] = v[first + child];
+        hole = child;
+    }
+    if ((len & 1) == 0 && child == (len - 2) / 2) {
+        child = 2 * (child + 1);
+        v[first + hole] = v[first + child - 1];
+        hole = child - 1;
+    }
+    iso_push_heap(v, first, hole, top, value, comp);
+}
+
+template <class Comp>
+__host__ __device__ inline void iso_heap_sort(int* v, int first, int last, Comp comp) {
+    // __partial_sort(first, last, last): __heap_select == make_heap, then __sort_heap
+    const int len = last - first;
+    if (len >= 2) {
+        int parent = (len - 2) / 2;
+        while (true) {
+            const int value = v[first + parent];
+            iso_adjust_heap(v, first, parent, len, value, comp);
+            if (parent == 0) break;
+            parent--;
+        }
+    }
+    int l = last;
+    while (l - first > 1) {
+        --l;
+        const int value = v[l];
+        v[l] = v[first];
+        iso_adjust_heap(v, first, 0, l - first, value, comp);
+    }
+}
+
+template <class Comp>
+__host__ __device__ inline void iso_move_median_to_first(int* v, int result, int a, int b, int c, Comp comp) {
+    if (comp(v[a], v[b])) {
+        if (comp(v[b], v[c])) iso_swap(v, result, b, comp);
+        else if (comp(v[a], v[c])) iso_swap(v, result, c, comp);
+        else iso_swap(v, result, a, comp);
+    } else if (comp(v[a], v[c])) iso_swap(v, result, a, comp);
+    else if (comp(v[b], v[c])) iso_swap(v, result, c, comp);
+    else iso_swap(v, result, b, comp);
+}
+
+template <class Comp>
+__host__ __device__ inline int iso_unguarded_partition(int* v, int first, int last, int pivot, Comp comp) {
+    while (true) {
+        while (comp(v[first], v[pivot])) ++first;
+        --last;
+        while (comp(v[pivot], v[last])) --last;
+        if (!(first < last)) return first;
+        iso_swap(v, first, last, comp);
+        ++first;
+    }
+}
+
+template <class Comp>
+__host__ __device__ inline void iso_unguarded_linear_insert(int* v, int last, Comp comp) {
+    const int val = v[last];
+    int next = last - 1;
+    while (comp(val, v[next])) {
+        v[last] = v[next];
+        last = next;
+        --next;
+    }
+    v[last] = val;
+}
+
+template <class Comp>
+__host__ __device__ inline void iso_insertion_sort(int* v, int first, int last, Comp comp) {
+    if (first == last) return;
+    for (int i = first + 1; i != last; ++i) {
+        if (comp(v[i], v[first])) {
+            const int val = v[i];
+            for (int j = i; j > first; --j) v[j] = v[j - 1];   // move_backward(first, i, i + 1)
+            v[first] = val;
+        } else {
+            iso_unguarded_linear_insert(v, i, comp);
+        }
+    }
+}
+
+// std::sort(v, v + n, comp) — same element moves as libstdc++.
+template <class Comp>
+__host__ __device__ inline void std_sort_indices(int* v, int n, Comp comp) {
+    if (n <= 0) return;
+    // __introsort_loop with an explicit stack (the recursion is on the right part)
+    int lg = 0;
+    for (int t = n; t > 1; t >>= 1) ++lg;
+    int stack_first[64], stack_last[64], stack_depth[64];
+    int sp = 0;
+    stack_first[0] = 0; stack_last[0] = n; stack_depth[0] = 2 * lg; sp = 1;
+    while (sp > 0) {
+        --sp;
+        int first = stack_first[sp], last = stack_last[sp], depth = stack_depth[sp];
+        // NOTE: libstdc++ recurses on [cut,last) *before* continuing with [first,cut); the two parts
+        // are disjoint, so processing order does not change the result.
+        while (last - first > 16) {
+            if (depth == 0) {
+                iso_heap_sort(v, first, last, comp);
+                last = first;
+                break;
+            }
+            --depth;
+            const int mid = first + (last - first) / 2;
+            iso_move_median_to_first(v, first, first + 1, mid, last - 1, comp);
+            const int cut = iso_unguarded_partition(v, first + 1, last, first, comp);
+            stack_first[sp] = cut; stack_last[sp] = last; stack_depth[sp] = depth; ++sp;
+            last = cut;
+        }
+    }
+    // __final_insertion_sort
+    if (n > 16) {
+        iso_insertion_sort(v, 0, 16, comp);
+        for (int i = 16; i != n; ++i) iso_unguarded_linear_insert(v, i, comp);
+    } else {
+        iso_insertion_sort(v, 0, n, comp);
+    }
+}
+
+}  // namespace vs

@@ -1,0 +1,84 @@
+// Host-callable launchers of the vs_tracker CUDA kernels (one .cu per stage).
+#pragma once
+#include "vs_common.cuh"
+
+namespace vs {
+
+void set_error(const char* fmt, ...);
+
+// ---- clahe.cu (K1, K2) ----
+void launch_clahe(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,
+                  int64_t dst_stride, int W, int H, int n_streams, uint8_t* luts, cudaStream_t st,
+                  int64_t* launches);
+void launch_clahe_lut_only(const uint8_t* src, int src_pitch, int64_t src_stride, int W, int H, int n_streams,
+                           uint8_t* luts, cudaStream_t st);
+void launch_clahe_apply_only(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,
+                             int64_t dst_stride, int W, int H, int n_streams, const uint8_t* luts,
+                             cudaStream_t st);
+void launch_copy_image(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,
+                       int64_t dst_stride, int W, int H, int n_streams, cudaStream_t st, int64_t* launches);
+
+// ---- pyramid.cu (K3) ----
+void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from, int n_streams, cudaStream_t st,
+                     int64_t* launches);
+
+// ---- lk.cu (K9) ----
+struct LkParams {
+    const uint8_t* prev_pyr;
+    const uint8_t* next_pyr;
+    PyrDesc pd;
+    int n_levels;             // levels used = min(built prev, built next, maxLevel + 1)
+    int win;
+    int max_count;            // min(max(lk_iterations, 0), 100)
+    double eps2;              // clamp(lk_eps, 0, 10)^2
+    float min_eig_threshold;  // 1e-4
+    const float2* pts;        // [n_streams][cap]
+    const int* counts;        // [n_streams]
+    int cap;
+    float2* next_pts;         // [n_streams][cap]
+    uint8_t* status;          // [n_streams][cap] raw LK status
+};
+int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches);
+
+// ---- shitomasi.cu (K5, K6) ----
+struct EigParams {
+    const uint8_t* img;       // level 0 of the new pyramid
+    int pitch;
+    int64_t img_stride;
+    const uint8_t* mask;      // [n_streams][H][mask_pitch]
+    int mask_pitch;
+    int64_t mask_stride;
+    int W, H;
+    const int* want;          // [n_streams] corners wanted; streams with want <= 0 are skipped (may be null)
+    unsigned int* max_enc;    // [n_streams] order-preserving encoding of the masked max
+    unsigned long long* cand; // [n_streams][cand_cap] (eig bits << 32 | y*W + x)
+    int* cand_count;          // [n_streams]
+    int cand_cap;
+    float* eig_out;           // optional dense eig map [n_streams][H][W] (stage tests), else null
+    double quality;           // 0.01
+};
+void launch_eig_max(const EigParams& p, int n_streams, cudaStream_t st, int64_t* launches);
+void launch_eig_candidates(const EigParams& p, int n_streams, cudaStream_t st, int64_t* launches);
+
+__host__ __device__ inline unsigned int float_order_enc(float f) {
+#ifdef __CUDA_ARCH__
+    const unsigned int b = __float_as_uint(f);
+#else
+    union { float f; unsigned int u; } cv; cv.f = f; const unsigned int b = cv.u;
+#endif
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ inline float float_order_dec(unsigned int e) {
+    const unsigned int b = (e & 0x80000000u) ? (e & 0x7fffffffu) : ~e;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(b);
+#else
+    union { float f; unsigned int u; } cv; cv.u = b; return cv.f;
+#endif
+}
+
+// ---- glue.cu (K8, K10, K7, K11) ----
+struct StreamState;   // defined in glue.cuh
+struct GlueParams;
+
+}  // namespace vs

@@ -1,0 +1,236 @@
+// K9 — sparse pyramidal Lucas-Kanade, one warp per feature, all pyramid levels in one launch.
+// Replaces cv::calcOpticalFlowPyrLK at /root/reference/src/frontend/feature_tracker.cpp:130-136
+// (pyramid inputs, flags = 0, minEigThreshold = 1e-4).  Arithmetic spec: SURVEY.md S3 —
+// 14-bit fixed-point bilinear weights, int16 template/gradient patches, exact integer accumulation
+// of the 2x2 gradient matrix and mismatch vector (order independent), float32 2x2 solve.
+//
+// The Scharr derivative images OpenCV precomputes are derived here from the staged u8 tile:
+// derivative = 0 where the derivative sample lies outside the level (BORDER_CONSTANT), while image
+// samples outside the level are REFLECT_101 — exactly the padding buildOpticalFlowPyramid applies.
+#include "kernels.h"
+
+namespace vs {
+
+constexpr int kLkMargin = 5;          // search tile = window + 2*margin
+constexpr int kLkWarpsPerCta = 8;
+
+__host__ __device__ inline int lk_tile_size(int win) { return win + 1 + 2 * kLkMargin; }
+__host__ __device__ inline int lk_tile_pitch(int win) { return (lk_tile_size(win) + 3) & ~3; }
+__host__ __device__ inline int lk_warp_smem(int win) {
+    return lk_tile_size(win) * lk_tile_pitch(win) + 4 * (win + 1) * (win + 1);
+}
+
+__device__ __forceinline__ long long warp_sum_exact(int v) {
+    // exact 64-bit sum of 32 int32 values with two REDUX ops (16-bit halves cannot overflow)
+    const int lo = v & 0xffff;
+    const int hi = v >> 16;
+    const int slo = __reduce_add_sync(0xffffffffu, lo);
+    const int shi = __reduce_add_sync(0xffffffffu, hi);
+    return ((long long)shi << 16) + (long long)slo;
+}
+
+__device__ __forceinline__ void lk_weights(float a, float b, int& w00, int& w01, int& w10, int& w11) {
+    const float a1 = __fsub_rn(1.0f, a), b1 = __fsub_rn(1.0f, b);
+    w00 = __float2int_rn(__fmul_rn(__fmul_rn(a1, b1), 16384.0f));
+    w01 = __float2int_rn(__fmul_rn(__fmul_rn(a, b1), 16384.0f));
+    w10 = __float2int_rn(__fmul_rn(__fmul_rn(a1, b), 16384.0f));
+    w11 = 16384 - w00 - w01 - w10;
+}
+
+__device__ __forceinline__ void stage_tile(uint8_t* tile, int tpitch, int rows, int cols,
+                                           const uint8_t* __restrict__ img, int w, int h, int pitch, int x0,
+                                           int y0, int lane) {
+    const bool interior = (x0 >= 0) && (y0 >= 0) && (x0 + cols <= w) && (y0 + rows <= h);
+    if (interior) {
+        for (int idx = lane; idx < rows * cols; idx += 32) {
+            const int r = idx / cols, c = idx - r * cols;
+            tile[r * tpitch + c] = __ldg(img + (int64_t)(y0 + r) * pitch + x0 + c);
+        }
+    } else {
+        for (int idx = lane; idx < rows * cols; idx += 32) {
+            const int r = idx / cols, c = idx - r * cols;
+            const int gy = reflect101(y0 + r, h), gx = reflect101(x0 + c, w);
+            tile[r * tpitch + c] = __ldg(img + (int64_t)gy * pitch + gx);
+        }
+    }
+}
+
+template <int WIN>
+__global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_kernel(LkParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int win = WIN ? WIN : p.win;
+    constexpr int KMAX = WIN ? (WIN * WIN + 31) / 32 : (kMaxWin * kMaxWin + 31) / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int s = blockIdx.y;
+    const int i = blockIdx.x * kLkWarpsPerCta + warp;
+    const int n = p.counts[s];
+    if (i >= n) return;
+
+    const int ts = lk_tile_size(win), tp = lk_tile_pitch(win);
+    uint8_t* tile = smem + warp * lk_warp_smem(win);
+    short2* deriv = reinterpret_cast<short2*>(tile + ts * tp);
+    const int dw = win + 1;
+    const int npx = win * win;
+    const float hw = (float)(win - 1) * 0.5f;
+
+    const float2 pt = p.pts[(int64_t)s * p.cap + i];
+    float2 next = make_float2(0.f, 0.f);
+    int status = 1;
+    const uint8_t* prev_base = p.prev_pyr + (int64_t)s * p.pd.stream_bytes;
+    const uint8_t* next_base = p.next_pyr + (int64_t)s * p.pd.stream_bytes;
+
+    int Iv[KMAX];        // interpolated template intensity (<= 8160)
+    int Gv[KMAX];        // packed (Ix | Iy << 16), each in [-4080, 4080]
+
+    for (int level = p.n_levels - 1; level >= 0; --level) {
+        const LevelDesc L = p.pd.lv[level];
+        const float lscale = 1.0f / (float)(1 << level);
+        const float2 prev_pt = make_float2(__fmul_rn(pt.x, lscale), __fmul_rn(pt.y, lscale));
+        if (level == p.n_levels - 1) next = prev_pt;
+        else next = make_float2(__fmul_rn(next.x, 2.0f), __fmul_rn(next.y, 2.0f));
+
+        const float ppx = __fsub_rn(prev_pt.x, hw), ppy = __fsub_rn(prev_pt.y, hw);
+        const int ipx = (int)floorf(ppx), ipy = (int)floorf(ppy);
+        if (ipx < -win || ipx >= L.w || ipy < -win || ipy >= L.h) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        int w00, w01, w10, w11;
+        lk_weights(__fsub_rn(ppx, (float)ipx), __fsub_rn(ppy, (float)ipy), w00, w01, w10, w11);
+
+        // ---- template: stage (win+3)^2 tile at (ipx-1, ipy-1), derive Scharr, interpolate ----
+        __syncwarp();
+        stage_tile(tile, tp, win + 3, win + 3, prev_base + L.offset, L.w, L.h, L.pitch, ipx - 1, ipy - 1, lane);
+        __syncwarp();
+        for (int idx = lane; idx < dw * dw; idx += 32) {
+            const int r = idx / dw, c = idx - r * dw;
+            const int gx = ipx + c, gy = ipy + r;
+            short2 d = make_short2(0, 0);
+            if (gx >= 0 && gx < L.w && gy >= 0 && gy < L.h) {
+                const uint8_t* t0 = tile + r * tp + c;
+                const uint8_t* t1 = t0 + tp;
+                const uint8_t* t2 = t1 + tp;
+                const int a00 = t0[0], a01 = t0[1], a02 = t0[2];
+                const int a10 = t1[0], a12 = t1[2];
+                const int a20 = t2[0], a21 = t2[1], a22 = t2[2];
+                d.x = (short)(3 * (a02 + a22 - a00 - a20) + 10 * (a12 - a10));
+                d.y = (short)(3 * (a20 + a22 - a00 - a02) + 10 * (a21 - a01));
+            }
+            deriv[idx] = d;
+        }
+        __syncwarp();
+        int s11 = 0, s12 = 0, s22 = 0;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            const int q = lane + 32 * k;
+            Iv[k] = 0;
+            Gv[k] = 0;
+            if (q < npx) {
+                const int y = q / win, x = q - y * win;
+                const uint8_t* t = tile + (y + 1) * tp + (x + 1);
+                const int iv = (t[0] * w00 + t[1] * w01 + t[tp] * w10 + t[tp + 1] * w11 + 256) >> 9;
+                const short2 d00 = deriv[y * dw + x], d01 = deriv[y * dw + x + 1];
+                const short2 d10 = deriv[(y + 1) * dw + x], d11 = deriv[(y + 1) * dw + x + 1];
+                const int ix = (d00.x * w00 + d01.x * w01 + d10.x * w10 + d11.x * w11 + 8192) >> 14;
+                const int iy = (d00.y * w00 + d01.y * w01 + d10.y * w10 + d11.y * w11 + 8192) >> 14;
+                Iv[k] = iv;
+                Gv[k] = (ix & 0xffff) | (iy << 16);
+                s11 += ix * ix;
+                s12 += ix * iy;
+                s22 += iy * iy;
+            }
+        }
+        const float kScale = 1.0f / (float)(1 << 20);
+        const float A11 = __fmul_rn(__ll2float_rn(warp_sum_exact(s11)), kScale);
+        const float A12 = __fmul_rn(__ll2float_rn(warp_sum_exact(s12)), kScale);
+        const float A22 = __fmul_rn(__ll2float_rn(warp_sum_exact(s22)), kScale);
+        float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
+        const float dA = __fsub_rn(A11, A22);
+        const float disc = __fadd_rn(__fmul_rn(dA, dA), __fmul_rn(__fmul_rn(4.0f, A12), A12));
+        const float min_eig = __fdiv_rn(__fsub_rn(__fadd_rn(A22, A11), __fsqrt_rn(disc)), (float)(2 * win * win));
+        if (min_eig < p.min_eig_threshold || D < 1.1920928955078125e-07f) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        D = __fdiv_rn(1.0f, D);
+
+        // ---- iterations on the next image ----
+        float qx = __fsub_rn(next.x, hw), qy = __fsub_rn(next.y, hw);
+        float pdx = 0.f, pdy = 0.f;
+        const uint8_t* J = next_base + L.offset;
+        int tox = 0, toy = 0;
+        bool staged = false;
+        for (int j = 0; j < p.max_count; ++j) {
+            const int iqx = (int)floorf(qx), iqy = (int)floorf(qy);
+            if (iqx < -win || iqx >= L.w || iqy < -win || iqy >= L.h) {
+                if (level == 0) status = 0;
+                break;
+            }
+            if (!staged || iqx < tox || iqx > tox + 2 * kLkMargin || iqy < toy || iqy > toy + 2 * kLkMargin) {
+                tox = iqx - kLkMargin;
+                toy = iqy - kLkMargin;
+                __syncwarp();
+                stage_tile(tile, tp, ts, ts, J, L.w, L.h, L.pitch, tox, toy, lane);
+                __syncwarp();
+                staged = true;
+            }
+            lk_weights(__fsub_rn(qx, (float)iqx), __fsub_rn(qy, (float)iqy), w00, w01, w10, w11);
+            const uint8_t* tb = tile + (iqy - toy) * tp + (iqx - tox);
+            int sb1 = 0, sb2 = 0;
+#pragma unroll
+            for (int k = 0; k < KMAX; ++k) {
+                const int q = lane + 32 * k;
+                if (q < npx) {
+                    const int y = q / win, x = q - y * win;
+                    const uint8_t* t = tb + y * tp + x;
+                    const int jv = (t[0] * w00 + t[1] * w01 + t[tp] * w10 + t[tp + 1] * w11 + 256) >> 9;
+                    const int diff = jv - Iv[k];
+                    const int ix = (int)(short)(Gv[k] & 0xffff), iy = Gv[k] >> 16;
+                    sb1 += diff * ix;
+                    sb2 += diff * iy;
+                }
+            }
+            const float b1 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb1)), kScale);
+            const float b2 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb2)), kScale);
+            const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
+            const float dy = __fmul_rn(__fsub_rn(__fmul_rn(A12, b1), __fmul_rn(A11, b2)), D);
+            qx = __fadd_rn(qx, dx);
+            qy = __fadd_rn(qy, dy);
+            next = make_float2(__fadd_rn(qx, hw), __fadd_rn(qy, hw));
+            if ((double)dx * (double)dx + (double)dy * (double)dy <= p.eps2) break;
+            if (j > 0 && fabs((double)__fadd_rn(dx, pdx)) < 0.01 && fabs((double)__fadd_rn(dy, pdy)) < 0.01) {
+                next.x = __fsub_rn(next.x, __fmul_rn(dx, 0.5f));
+                next.y = __fsub_rn(next.y, __fmul_rn(dy, 0.5f));
+                break;
+            }
+            pdx = dx;
+            pdy = dy;
+        }
+    }
+    if (lane == 0) {
+        p.next_pts[(int64_t)s * p.cap + i] = next;
+        p.status[(int64_t)s * p.cap + i] = (uint8_t)status;
+    }
+}
+
+int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches) {
+    if (p.win < 3 || p.win > kMaxWin || (p.win & 1) == 0) return -1;
+    if (max_features <= 0 || p.n_levels <= 0) return 0;
+    const int smem = kLkWarpsPerCta * lk_warp_smem(p.win);
+    dim3 grid((max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta, n_streams);
+    if (p.win == 21) {
+        lk_kernel<21><<<grid, 32 * kLkWarpsPerCta, smem, st>>>(p);
+    } else {
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaFuncSetAttribute(lk_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 kLkWarpsPerCta * lk_warp_smem(kMaxWin));
+            attr_set = true;
+        }
+        lk_kernel<0><<<grid, 32 * kLkWarpsPerCta, smem, st>>>(p);
+    }
+    if (launches) *launches += 1;
+    return 0;
+}
+
+}  // namespace vs

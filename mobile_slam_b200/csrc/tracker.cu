@@ -1,0 +1,926 @@
+// Host layer of the B200 visual front-end: the C ABI of include/vs_tracker.h over CUDA streams.
+// Mirrors frontend::FeatureTracker (include/frontend/feature_tracker.h:25-76 of the reference):
+// one handle = n_streams independent trackers whose per-frame work is batched into the same launches.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../include/vs_tracker.h"
+#include "glue.cuh"
+
+namespace vs {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// OpenCV's filled-circle row half-widths (cv::circle, thickness -1, LINE_8): integer midpoint
+// rasteriser, SURVEY.md S5.  hw[|dy|] = -1 when the row is not painted.
+static std::vector<int> circle_half_widths(int radius) {
+    std::vector<int> hw(radius + 1, -1);
+    int dx = radius, dy = 0, err = 0, plus = 1, minus = (radius << 1) - 1;
+    while (dx >= dy) {
+        if (dy <= radius && hw[dy] < dx) hw[dy] = dx;
+        if (dx <= radius && hw[dx] < dy) hw[dx] = dy;
+        dy++;
+        err += plus;
+        plus += 2;
+        const int mask = (err <= 0) - 1;
+        err -= minus & mask;
+        dx += mask;
+        minus -= mask & 2;
+    }
+    return hw;
+}
+
+static inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
+
+struct DeviceArena {
+    std::vector<void*> blocks;
+    template <class T>
+    cudaError_t alloc(T** p, size_t count, bool zero = true) {
+        void* q = nullptr;
+        cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 256);
+        if (e != cudaSuccess) return e;
+        blocks.push_back(q);
+        if (zero) {
+            e = cudaMemset(q, 0, count * sizeof(T) + 256);
+            if (e != cudaSuccess) return e;
+        }
+        *p = reinterpret_cast<T*>(q);
+        return cudaSuccess;
+    }
+    void release() {
+        for (void* b : blocks) cudaFree(b);
+        blocks.clear();
+    }
+};
+
+}  // namespace vs
+
+using namespace vs;
+
+struct vs_tracker {
+    vs_tracker_config cfg{};
+    int B = 0, W = 0, H = 0, cap = 0;
+    int raw_pitch = 0;
+    int64_t raw_stride = 0;
+    PyrDesc pd{};                 // geometry of every possible level (kMaxLevels)
+    int built[2] = {0, 0};        // levels built in each pyramid buffer
+    int cur = 0;                  // index of the reference (previous-frame) pyramid
+    bool has_prev = false;
+    int n_bound = 0;              // upper bound of per-stream feature counts (LK grid size)
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+    int64_t launches = 0;
+    DeviceArena arena;
+    uint8_t* d_raw = nullptr;
+    uint8_t* d_pyr[2] = {nullptr, nullptr};
+    uint8_t* d_luts = nullptr;
+    uint8_t* d_base_mask = nullptr;
+    int* d_disc_hw = nullptr;
+    double* d_cur_time = nullptr;
+    float* d_eig = nullptr;       // lazily allocated dense eig map (stage API only)
+    GlueParams g{};
+    // pinned host mirrors
+    uint8_t* h_block = nullptr;   // results: hdr | ids | cnt | pts | un | vel
+    size_t h_block_bytes = 0;
+    uint8_t* d_rblock = nullptr;
+    double* h_time = nullptr;
+    // RANSAC callback hop
+    vs_reject_fn reject_fn = nullptr;
+    void* reject_user = nullptr;
+    int* h_wn = nullptr;
+    int* h_flag = nullptr;
+    float2* h_lcur = nullptr;
+    float2* h_lnext = nullptr;
+    float2* h_wnext = nullptr;
+    uint8_t* h_rstatus = nullptr;
+    std::vector<int> disc_hw_host;
+    int disc_radius = -1;
+};
+
+namespace vs {
+
+static void plan_pyramid(vs_tracker* t) {
+    PyrDesc& pd = t->pd;
+    int w = t->W, h = t->H;
+    int64_t off = 0;
+    pd.n_levels = kMaxLevels;
+    for (int l = 0; l < kMaxLevels; ++l) {
+        pd.lv[l].w = w;
+        pd.lv[l].h = h;
+        pd.lv[l].pitch = round_up(w, 16);
+        pd.lv[l].offset = off;
+        off += (int64_t)round_up(pd.lv[l].pitch * h, 256);
+        w = (w + 1) / 2;
+        h = (h + 1) / 2;
+        if (w < 1) w = 1;
+        if (h < 1) h = 1;
+    }
+    pd.stream_bytes = off;
+}
+
+// levels cv::buildOpticalFlowPyramid would produce for (winSize, maxLevel)
+static int levels_to_build(const vs_tracker* t) {
+    int n = 1;
+    int w = t->W, h = t->H;
+    for (int l = 0; l < t->cfg.lk_pyramid_levels && l + 1 < kMaxLevels; ++l) {
+        const int nw = (w + 1) / 2, nh = (h + 1) / 2;
+        if (nw <= t->cfg.lk_window_size || nh <= t->cfg.lk_window_size) break;
+        w = nw;
+        h = nh;
+        ++n;
+    }
+    return n;
+}
+
+static void fill_camera(const vs_camera& c, CameraDev& d) {
+    memset(&d, 0, sizeof(d));
+    d.model = c.model_type;
+    if (c.model_type != VS_CAM_SCARAMUZZA) {
+        d.inv_K11 = 1.0 / c.fx;
+        d.inv_K13 = -c.cx / c.fx;
+        d.inv_K22 = 1.0 / c.fy;
+        d.inv_K23 = -c.cy / c.fy;
+    }
+    for (int i = 0; i < 4; ++i) d.d[i] = c.d[i];
+    d.xi = c.xi;
+    for (int i = 0; i < 5; ++i) d.poly[i] = c.poly[i];
+    d.cx = c.cx;
+    d.cy = c.cy;
+    d.aff_c = c.aff_c;
+    d.aff_d = c.aff_d;
+    d.aff_e = c.aff_e;
+    const double det = c.aff_c - c.aff_d * c.aff_e;
+    d.inv_scale = det != 0.0 ? 1.0 / det : 0.0;
+    d.no_distortion = (c.d[0] == 0.0 && c.d[1] == 0.0 && c.d[2] == 0.0 && c.d[3] == 0.0) ? 1 : 0;
+    int npow = 9;   // EquidistantCamera::backprojectSymmetric, EquidistantCamera.cc:585-597
+    if (c.d[3] == 0.0) npow -= 2;
+    if (c.d[2] == 0.0) npow -= 2;
+    if (c.d[1] == 0.0) npow -= 2;
+    if (c.d[0] == 0.0) npow -= 2;
+    d.kb_npow = npow;
+}
+
+static int upload_disc(vs_tracker* t) {
+    const int r = t->cfg.min_dist;
+    if (r == t->disc_radius) return VS_OK;
+    t->disc_hw_host = circle_half_widths(r);
+    VS_CUDA_TRY(cudaMemcpyAsync(t->d_disc_hw, t->disc_hw_host.data(), sizeof(int) * (r + 1), cudaMemcpyHostToDevice,
+                                t->stream));
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    t->disc_radius = r;
+    return VS_OK;
+}
+
+static void sync_glue_params(vs_tracker* t) {
+    GlueParams& g = t->g;
+    g.max_cnt = t->cfg.max_cnt;
+    g.min_dist = t->cfg.min_dist;
+    g.ransac_enabled = t->cfg.ransac_mode != VS_RANSAC_OFF;
+    g.focal_length = t->cfg.focal_length;
+    g.f_threshold = t->cfg.f_threshold;
+    g.f_edge_factor = t->cfg.f_threshold_edge_factor;
+    g.fb_check = t->cfg.fb_check;
+    g.fb_threshold = (float)t->cfg.fb_threshold;
+}
+
+}  // namespace vs
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+const char* vs_last_error(void) { return vs::g_err; }
+int vs_abi_version(void) { return VS_ABI_VERSION; }
+
+void vs_tracker_default_config(vs_tracker_config* c) {
+    if (!c) return;
+    memset(c, 0, sizeof(*c));
+    c->struct_size = (int32_t)sizeof(*c);
+    c->n_streams = 1;
+    c->width = 752;                 // include/utility/config.h:18-30 defaults
+    c->height = 480;
+    c->focal_length = 460.0;
+    c->max_cnt = 150;
+    c->min_dist = 30;
+    c->f_threshold = 1.0;
+    c->f_threshold_edge_factor = 0.0;
+    c->equalize = 1;
+    c->fisheye = 0;
+    c->lk_window_size = 21;
+    c->lk_pyramid_levels = 3;
+    c->lk_iterations = 30;
+    c->lk_eps = 0.01;
+    c->fb_check = 0;
+    c->fb_threshold = 0.5;
+    c->ransac_mode = VS_RANSAC_DEVICE;
+    c->camera.model_type = VS_CAM_PINHOLE;
+    c->camera.width = 752;
+    c->camera.height = 480;
+    c->camera.fx = c->camera.fy = 460.0;
+    c->camera.cx = 376.0;
+    c->camera.cy = 240.0;
+    c->camera.aff_c = 1.0;
+}
+
+static const int kMaxDiscRadius = 1024;
+
+int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective, vs_tracker** out) {
+    if (!cfg || !out) { set_error("vs_tracker_create: null argument"); return VS_ERR_INVALID; }
+    *out = nullptr;
+    if (cfg->struct_size != (int32_t)sizeof(vs_tracker_config)) {
+        set_error("vs_tracker_create: struct_size %d != %d (ABI mismatch)", cfg->struct_size, (int)sizeof(vs_tracker_config));
+        return VS_ERR_INVALID;
+    }
+    if (cfg->n_streams < 1 || cfg->width < 32 || cfg->height < 32 || cfg->width > 16384 || cfg->height > 16384) {
+        set_error("vs_tracker_create: bad n_streams/width/height");
+        return VS_ERR_INVALID;
+    }
+    if (cfg->max_cnt < 1 || cfg->min_dist < 1 || cfg->min_dist > kMaxDiscRadius) {
+        set_error("vs_tracker_create: bad max_cnt/min_dist");
+        return VS_ERR_INVALID;
+    }
+    if (cfg->lk_window_size < 3 || cfg->lk_window_size > kMaxWin || (cfg->lk_window_size & 1) == 0) {
+        set_error("vs_tracker_create: lk_window_size must be odd and in [3,%d]", kMaxWin);
+        return VS_ERR_INVALID;
+    }
+    if (cfg->lk_pyramid_levels < 0 || cfg->lk_pyramid_levels > kMaxLevels - 1) {
+        set_error("vs_tracker_create: lk_pyramid_levels must be in [0,%d]", kMaxLevels - 1);
+        return VS_ERR_INVALID;
+    }
+    if (cfg->camera.model_type < 0 || cfg->camera.model_type > 3) {
+        set_error("vs_tracker_create: unknown camera model %d", cfg->camera.model_type);
+        return VS_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        set_error("vs_tracker_create: no CUDA device (this library has no CPU fallback)");
+        return VS_ERR_CUDA;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) { set_error("vs_tracker_create: bad device %d", cfg->device); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(cfg->device));
+
+    vs_tracker* t = new (std::nothrow) vs_tracker();
+    if (!t) { set_error("out of host memory"); return VS_ERR_NOMEM; }
+    t->cfg = *cfg;
+    t->cfg.fisheye_mask_image = nullptr;
+    t->B = cfg->n_streams;
+    t->W = cfg->width;
+    t->H = cfg->height;
+    int cap = cfg->capacity > 0 ? cfg->capacity : (cfg->max_cnt > 256 ? cfg->max_cnt : 256);
+    if (cap < cfg->max_cnt) cap = cfg->max_cnt;
+    cap = round_up(cap, 32);
+    if (cap > 32768) { delete t; set_error("capacity too large"); return VS_ERR_CAPACITY; }
+    t->cap = cap;
+    t->cfg.capacity = cap;
+    t->n_bound = cfg->max_cnt;
+    plan_pyramid(t);
+    t->raw_pitch = round_up(t->W, 16);
+    t->raw_stride = (int64_t)round_up(t->raw_pitch * t->H, 256);
+
+#define VS_TRY_CREATE(expr)                                                                      \
+    do {                                                                                         \
+        cudaError_t _e = (expr);                                                                 \
+        if (_e != cudaSuccess) {                                                                 \
+            set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));     \
+            vs_tracker_destroy(t);                                                               \
+            return _e == cudaErrorMemoryAllocation ? VS_ERR_NOMEM : VS_ERR_CUDA;                 \
+        }                                                                                        \
+    } while (0)
+
+    VS_TRY_CREATE(cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking));
+    VS_TRY_CREATE(cudaEventCreate(&t->ev0));
+    VS_TRY_CREATE(cudaEventCreate(&t->ev1));
+    const int64_t B = t->B, C = t->cap;
+    GlueParams& g = t->g;
+    g.n_streams = t->B;
+    g.cap = t->cap;
+    g.W = t->W;
+    g.H = t->H;
+    fill_camera(cfg->camera, g.cam);
+    sync_glue_params(t);
+    DeviceArena& A = t->arena;
+    VS_TRY_CREATE(A.alloc(&t->d_raw, (size_t)(B * t->raw_stride)));
+    VS_TRY_CREATE(A.alloc(&t->d_pyr[0], (size_t)(B * t->pd.stream_bytes)));
+    VS_TRY_CREATE(A.alloc(&t->d_pyr[1], (size_t)(B * t->pd.stream_bytes)));
+    VS_TRY_CREATE(A.alloc(&t->d_luts, (size_t)(B * 64 * 256)));
+    VS_TRY_CREATE(A.alloc(&t->d_disc_hw, (size_t)kMaxDiscRadius + 1));
+    VS_TRY_CREATE(A.alloc(&t->d_cur_time, (size_t)B));
+    g.cur_time = t->d_cur_time;
+    VS_TRY_CREATE(A.alloc(&g.n, B));
+    VS_TRY_CREATE(A.alloc(&g.pts, B * C));
+    VS_TRY_CREATE(A.alloc(&g.ids, B * C));
+    VS_TRY_CREATE(A.alloc(&g.cnt, B * C));
+    VS_TRY_CREATE(A.alloc(&g.un, B * C));
+    VS_TRY_CREATE(A.alloc(&g.next_id, B));
+    VS_TRY_CREATE(A.alloc(&g.prev_time, B));
+    VS_TRY_CREATE(A.alloc(&g.lk_next, B * C));
+    VS_TRY_CREATE(A.alloc(&g.lk_status, B * C));
+    VS_TRY_CREATE(A.alloc(&g.lk_back, B * C));
+    VS_TRY_CREATE(A.alloc(&g.lk_back_status, B * C));
+    VS_TRY_CREATE(A.alloc(&g.wn, B));
+    VS_TRY_CREATE(A.alloc(&g.w_cur, B * C));
+    VS_TRY_CREATE(A.alloc(&g.w_next, B * C));
+    VS_TRY_CREATE(A.alloc(&g.w_ids, B * C));
+    VS_TRY_CREATE(A.alloc(&g.w_cnt, B * C));
+    VS_TRY_CREATE(A.alloc(&g.w_un, B * C));
+    VS_TRY_CREATE(A.alloc(&g.w_lcur, B * C));
+    VS_TRY_CREATE(A.alloc(&g.w_lnext, B * C));
+    VS_TRY_CREATE(A.alloc(&g.w_rstatus, B * C));
+    VS_TRY_CREATE(A.alloc(&g.ransac_flag, B));
+    VS_TRY_CREATE(A.alloc(&g.kn, B));
+    VS_TRY_CREATE(A.alloc(&g.k_pts, B * C));
+    VS_TRY_CREATE(A.alloc(&g.k_ids, B * C));
+    VS_TRY_CREATE(A.alloc(&g.k_cnt, B * C));
+    VS_TRY_CREATE(A.alloc(&g.k_un, B * C));
+    VS_TRY_CREATE(A.alloc(&g.want, B));
+    g.mask_pitch = round_up(t->W, 16);
+    g.mask_stride = (int64_t)round_up(g.mask_pitch * t->H, 256);
+    VS_TRY_CREATE(A.alloc(&g.mask, (size_t)(B * g.mask_stride)));
+    VS_TRY_CREATE(A.alloc(&t->d_base_mask, (size_t)g.mask_stride));
+    g.base_mask = t->d_base_mask;
+    g.disc_hw = t->d_disc_hw;
+    int cc = 1;
+    while (cc < (t->W * t->H + 3) / 4) cc <<= 1;       // strict 3x3 local maxima cannot exceed P/4
+    g.cand_cap = cc;
+    VS_TRY_CREATE(A.alloc(&g.cand, (size_t)(B * cc), false));
+    VS_TRY_CREATE(A.alloc(&g.cand_count, B));
+    VS_TRY_CREATE(A.alloc(&g.max_enc, B));
+    // results block: hdr | ids | cnt | pts | un | vel
+    t->h_block_bytes = (size_t)(B * kHdrInts * 4 + B * C * (4 + 4 + 8 + 8 + 8));
+    VS_TRY_CREATE(A.alloc(&t->d_rblock, t->h_block_bytes));
+    {
+        uint8_t* p = t->d_rblock;
+        g.r_hdr = reinterpret_cast<int*>(p); p += B * kHdrInts * 4;
+        g.r_ids = reinterpret_cast<int*>(p); p += B * C * 4;
+        g.r_cnt = reinterpret_cast<int*>(p); p += B * C * 4;
+        g.r_pts = reinterpret_cast<float2*>(p); p += B * C * 8;
+        g.r_un = reinterpret_cast<float2*>(p); p += B * C * 8;
+        g.r_vel = reinterpret_cast<float2*>(p);
+    }
+    VS_TRY_CREATE(cudaMallocHost(&t->h_block, t->h_block_bytes));
+    memset(t->h_block, 0, t->h_block_bytes);
+    VS_TRY_CREATE(cudaMallocHost(&t->h_time, sizeof(double) * B));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_wn, sizeof(int) * B));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_flag, sizeof(int) * B));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_lcur, sizeof(float2) * B * C));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_lnext, sizeof(float2) * B * C));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_wnext, sizeof(float2) * B * C));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_rstatus, (size_t)(B * C)));
+
+    // base mask: feature_tracker.cpp:40-60
+    {
+        std::vector<uint8_t> m((size_t)g.mask_stride, 0);
+        const int W = t->W, H = t->H, mp = g.mask_pitch;
+        if (cfg->fisheye && cfg->fisheye_mask_image) {
+            const int st = cfg->fisheye_mask_stride > 0 ? cfg->fisheye_mask_stride : W;
+            for (int y = 0; y < H; ++y) memcpy(&m[(size_t)y * mp], cfg->fisheye_mask_image + (size_t)y * st, W);
+        } else if (cfg->fisheye) {
+            const double cx = W / 2.0, cy = H / 2.0;
+            double rad = cx;
+            if (cy < rad) rad = cy;
+            if (W - cx < rad) rad = W - cx;
+            if (H - cy < rad) rad = H - cy;
+            rad *= 0.95;
+            const int icx = (int)cx, icy = (int)cy, r = (int)rad;
+            const std::vector<int> hw = circle_half_widths(r);
+            for (int dy = -r; dy <= r; ++dy) {
+                const int y = icy + dy, w = hw[dy < 0 ? -dy : dy];
+                if (y < 0 || y >= H || w < 0) continue;
+                int xa = icx - w, xb = icx + w;
+                if (xa < 0) xa = 0;
+                if (xb > W - 1) xb = W - 1;
+                for (int x = xa; x <= xb; ++x) m[(size_t)y * mp + x] = 255;
+            }
+        } else {
+            for (int y = 0; y < H; ++y) memset(&m[(size_t)y * mp], 255, W);
+        }
+        VS_TRY_CREATE(cudaMemcpy(t->d_base_mask, m.data(), m.size(), cudaMemcpyHostToDevice));
+    }
+    {
+        std::vector<int> ids((size_t)B, cfg->first_feature_id);
+        VS_TRY_CREATE(cudaMemcpy(g.next_id, ids.data(), sizeof(int) * B, cudaMemcpyHostToDevice));
+    }
+    if (upload_disc(t) != VS_OK) { vs_tracker_destroy(t); return VS_ERR_CUDA; }
+    VS_TRY_CREATE(cudaStreamSynchronize(t->stream));
+#undef VS_TRY_CREATE
+    if (effective) *effective = t->cfg;
+    *out = t;
+    return VS_OK;
+}
+
+void vs_tracker_destroy(vs_tracker* t) {
+    if (!t) return;
+    cudaSetDevice(t->cfg.device);
+    if (t->stream) cudaStreamSynchronize(t->stream);
+    t->arena.release();
+    if (t->d_eig) cudaFree(t->d_eig);
+    if (t->h_block) cudaFreeHost(t->h_block);
+    if (t->h_time) cudaFreeHost(t->h_time);
+    if (t->h_wn) cudaFreeHost(t->h_wn);
+    if (t->h_flag) cudaFreeHost(t->h_flag);
+    if (t->h_lcur) cudaFreeHost(t->h_lcur);
+    if (t->h_lnext) cudaFreeHost(t->h_lnext);
+    if (t->h_wnext) cudaFreeHost(t->h_wnext);
+    if (t->h_rstatus) cudaFreeHost(t->h_rstatus);
+    if (t->ev0) cudaEventDestroy(t->ev0);
+    if (t->ev1) cudaEventDestroy(t->ev1);
+    if (t->stream) cudaStreamDestroy(t->stream);
+    delete t;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// frame pipeline
+// =================================================================================================
+namespace vs {
+
+int launch_ransac(vs_tracker* t);   // ransac.cu
+
+static void fill_lk_params(vs_tracker* t, LkParams& p, int prev_buf, int next_buf, const float2* pts, float2* out,
+                           uint8_t* status) {
+    p.prev_pyr = t->d_pyr[prev_buf];
+    p.next_pyr = t->d_pyr[next_buf];
+    p.pd = t->pd;
+    int nl = t->built[prev_buf] < t->built[next_buf] ? t->built[prev_buf] : t->built[next_buf];
+    if (nl > t->cfg.lk_pyramid_levels + 1) nl = t->cfg.lk_pyramid_levels + 1;
+    p.n_levels = nl;
+    p.win = t->cfg.lk_window_size;
+    int mc = t->cfg.lk_iterations;            // TermCriteria clamps inside calcOpticalFlowPyrLK
+    mc = mc < 0 ? 0 : (mc > 100 ? 100 : mc);
+    p.max_count = mc;
+    double e = t->cfg.lk_eps;
+    e = e < 0.0 ? 0.0 : (e > 10.0 ? 10.0 : e);
+    p.eps2 = e * e;
+    p.min_eig_threshold = 1e-4f;
+    p.pts = pts;
+    p.counts = t->g.n;
+    p.cap = t->cap;
+    p.next_pts = out;
+    p.status = status;
+}
+
+// build the pyramid of the new frame into buffer `buf` from a device image
+static int build_pyramid(vs_tracker* t, int buf, const uint8_t* d_img, int pitch, int64_t stride) {
+    const LevelDesc& l0 = t->pd.lv[0];
+    if (t->cfg.equalize)
+        launch_clahe(d_img, pitch, stride, t->d_pyr[buf] + l0.offset, l0.pitch, t->pd.stream_bytes, t->W, t->H, t->B,
+                     t->d_luts, t->stream, &t->launches);
+    else
+        launch_copy_image(d_img, pitch, stride, t->d_pyr[buf] + l0.offset, l0.pitch, t->pd.stream_bytes, t->W, t->H,
+                          t->B, t->stream, &t->launches);
+    const int nl = levels_to_build(t);
+    for (int l = 0; l + 1 < nl; ++l) launch_pyr_down(t->d_pyr[buf], t->pd, l, t->B, t->stream, &t->launches);
+    t->built[buf] = nl;
+    return VS_OK;
+}
+
+static int ransac_callback_hop(vs_tracker* t) {
+    GlueParams& g = t->g;
+    const size_t B = t->B, C = t->cap;
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_wn, g.wn, sizeof(int) * B, cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_flag, g.ransac_flag, sizeof(int) * B, cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_lcur, g.w_lcur, sizeof(float2) * B * C, cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_lnext, g.w_lnext, sizeof(float2) * B * C, cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_wnext, g.w_next, sizeof(float2) * B * C, cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    bool any = false;
+    for (size_t s = 0; s < B; ++s) {
+        if (!t->h_flag[s]) continue;
+        any = true;
+        const int n = t->h_wn[s];
+        uint8_t* st = t->h_rstatus + s * C;
+        memset(st, 1, n);
+        if (t->reject_fn) {
+            const int rc = t->reject_fn(t->reject_user, (int)s, n, reinterpret_cast<const float*>(t->h_lcur + s * C),
+                                        reinterpret_cast<const float*>(t->h_lnext + s * C),
+                                        reinterpret_cast<const float*>(t->h_wnext + s * C), st);
+            if (rc != 0) { set_error("reject callback failed for stream %d (rc=%d)", (int)s, rc); return VS_ERR_STATE; }
+        }
+    }
+    if (any) VS_CUDA_TRY(cudaMemcpyAsync(g.w_rstatus, t->h_rstatus, B * C, cudaMemcpyHostToDevice, t->stream));
+    return VS_OK;
+}
+
+static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t stride) {
+    GlueParams& g = t->g;
+    sync_glue_params(t);
+    const int rc0 = upload_disc(t);
+    if (rc0 != VS_OK) return rc0;
+    if (t->n_bound < t->cfg.max_cnt) t->n_bound = t->cfg.max_cnt;
+    const int nb = 1 - t->cur;
+    build_pyramid(t, nb, d_img, pitch, stride);
+    if (t->has_prev) {
+        LkParams p;
+        fill_lk_params(t, p, t->cur, nb, g.pts, g.lk_next, g.lk_status);
+        if (launch_lk(p, t->B, t->n_bound, t->stream, &t->launches) != 0) { set_error("LK: unsupported window"); return VS_ERR_INVALID; }
+        if (t->cfg.fb_check) {
+            LkParams q;
+            fill_lk_params(t, q, nb, t->cur, g.lk_next, g.lk_back, g.lk_back_status);
+            launch_lk(q, t->B, t->n_bound, t->stream, &t->launches);
+        }
+    }
+    launch_post_lk(g, t->stream, &t->launches);
+    if (t->cfg.ransac_mode == VS_RANSAC_CALLBACK) {
+        const int rc = ransac_callback_hop(t);
+        if (rc != VS_OK) return rc;
+    } else if (t->cfg.ransac_mode == VS_RANSAC_DEVICE) {
+        const int rc = launch_ransac(t);
+        if (rc != VS_OK) return rc;
+    }
+    launch_set_mask(g, t->stream, &t->launches);
+    launch_paint_mask(g, t->stream, &t->launches);
+    EigParams e{};
+    e.img = t->d_pyr[nb] + t->pd.lv[0].offset;
+    e.pitch = t->pd.lv[0].pitch;
+    e.img_stride = t->pd.stream_bytes;
+    e.mask = g.mask;
+    e.mask_pitch = g.mask_pitch;
+    e.mask_stride = g.mask_stride;
+    e.W = t->W;
+    e.H = t->H;
+    e.want = g.want;
+    e.max_enc = g.max_enc;
+    e.cand = g.cand;
+    e.cand_count = g.cand_count;
+    e.cand_cap = g.cand_cap;
+    e.eig_out = nullptr;
+    e.quality = 0.01;
+    launch_eig_max(e, t->B, t->stream, &t->launches);
+    launch_eig_candidates(e, t->B, t->stream, &t->launches);
+    launch_select_finish(g, t->stream, &t->launches);
+    t->cur = nb;
+    t->has_prev = true;
+    VS_CUDA_TRY(cudaGetLastError());
+    return VS_OK;
+}
+
+static void fill_results(vs_tracker* t, vs_track_result* out) {
+    const int64_t B = t->B, C = t->cap;
+    const uint8_t* p = t->h_block;
+    const int* hdr = reinterpret_cast<const int*>(p); p += B * kHdrInts * 4;
+    const int* ids = reinterpret_cast<const int*>(p); p += B * C * 4;
+    const int* cnt = reinterpret_cast<const int*>(p); p += B * C * 4;
+    const float* pts = reinterpret_cast<const float*>(p); p += B * C * 8;
+    const float* un = reinterpret_cast<const float*>(p); p += B * C * 8;
+    const float* vel = reinterpret_cast<const float*>(p);
+    for (int64_t s = 0; s < B; ++s) {
+        const int* h = hdr + s * kHdrInts;
+        vs_track_result& r = out[s];
+        r.n = h[H_N];
+        r.n_new = h[H_NNEW];
+        r.ids = ids + s * C;
+        r.track_cnt = cnt + s * C;
+        r.cur_pts = pts + s * C * 2;
+        r.undist = un + s * C * 2;
+        r.velocity = vel + s * C * 2;
+        r.n_lk_in = h[H_LK_IN];
+        r.n_lk_ok = h[H_LK_OK];
+        r.n_ransac_in = h[H_RANSAC_IN];
+        r.n_ransac_out = h[H_RANSAC_OUT];
+        r.n_mask_kept = h[H_MASK_KEPT];
+        r.n_candidates = h[H_NCAND];
+        r.ransac_ran = h[H_RANSAC_RAN];
+        float f;
+        memcpy(&f, &h[H_RMS_BITS], 4);
+        r.rms_disp = f;
+    }
+}
+
+}  // namespace vs
+
+extern "C" {
+
+int vs_tracker_fetch_results(vs_tracker* t, vs_track_result* out) {
+    if (!t || !out) { set_error("null argument"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_block, t->d_rblock, t->h_block_bytes, cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    fill_results(t, out);
+    return VS_OK;
+}
+
+int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_t stride, int64_t image_stride_bytes,
+                                  const double* time_s, int32_t results_to_host, vs_track_result* out) {
+    if (!t || !d_frames || !time_s) { set_error("null argument"); return VS_ERR_INVALID; }
+    if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    memcpy(t->h_time, time_s, sizeof(double) * t->B);
+    VS_CUDA_TRY(cudaEventRecord(t->ev0, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->d_cur_time, t->h_time, sizeof(double) * t->B, cudaMemcpyHostToDevice, t->stream));
+    const uint8_t* img = d_frames;
+    int pitch = stride;
+    int64_t istride = image_stride_bytes;
+    if ((stride & 15) || (reinterpret_cast<uintptr_t>(d_frames) & 15) || (image_stride_bytes & 15)) {
+        // kernels use aligned vector loads: stage unaligned device input through the internal buffer
+        launch_copy_image(d_frames, stride, image_stride_bytes, t->d_raw, t->raw_pitch, t->raw_stride, t->W, t->H, t->B,
+                          t->stream, &t->launches);
+        img = t->d_raw;
+        pitch = t->raw_pitch;
+        istride = t->raw_stride;
+    }
+    const int rc = run_frame(t, img, pitch, istride);
+    if (rc != VS_OK) return rc;
+    VS_CUDA_TRY(cudaEventRecord(t->ev1, t->stream));
+    if (results_to_host && out) {
+        const int rc2 = vs_tracker_fetch_results(t, out);
+        if (rc2 != VS_OK) return rc2;
+        cudaEventElapsedTime(&t->last_ms, t->ev0, t->ev1);
+    }
+    return VS_OK;
+}
+
+int vs_tracker_track_batch(vs_tracker* t, const uint8_t* const* frames, int32_t stride, const double* time_s,
+                           vs_track_result* out) {
+    if (!t || !frames || !time_s || !out) { set_error("null argument"); return VS_ERR_INVALID; }
+    if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    for (int s = 0; s < t->B; ++s) {
+        if (!frames[s]) { set_error("frames[%d] is null", s); return VS_ERR_INVALID; }
+        VS_CUDA_TRY(cudaMemcpy2DAsync(t->d_raw + (int64_t)s * t->raw_stride, t->raw_pitch, frames[s], stride, t->W, t->H,
+                                      cudaMemcpyHostToDevice, t->stream));
+    }
+    return vs_tracker_track_batch_device(t, t->d_raw, t->raw_pitch, t->raw_stride, time_s, 1, out);
+}
+
+int vs_tracker_track(vs_tracker* t, const uint8_t* gray, int32_t stride, double time_s, vs_track_result* out) {
+    if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    if (t->B != 1) { set_error("vs_tracker_track needs n_streams == 1 (use vs_tracker_track_batch)"); return VS_ERR_STATE; }
+    const uint8_t* frames[1] = {gray};
+    return vs_tracker_track_batch(t, frames, stride, &time_s, out);
+}
+
+int vs_tracker_set_params(vs_tracker* t, int32_t max_cnt, int32_t min_dist, double f_threshold, int32_t lk_window,
+                          int32_t lk_pyramid, int32_t lk_iterations, double lk_eps, double f_edge_factor) {
+    if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    if (max_cnt > 0) {
+        if (max_cnt > t->cap) { set_error("max_cnt %d above handle capacity %d", max_cnt, t->cap); return VS_ERR_CAPACITY; }
+        t->cfg.max_cnt = max_cnt;
+    }
+    if (min_dist > 0) {
+        if (min_dist > kMaxDiscRadius) { set_error("min_dist too large"); return VS_ERR_INVALID; }
+        t->cfg.min_dist = min_dist;
+    }
+    if (f_threshold > 0.0) t->cfg.f_threshold = f_threshold;
+    if (lk_window > 0 && (lk_window % 2 == 1)) {       // same guard as VIOEngine::setTrackingParams
+        if (lk_window > kMaxWin || lk_window < 3) { set_error("lk_window above %d unsupported", kMaxWin); return VS_ERR_INVALID; }
+        t->cfg.lk_window_size = lk_window;
+    }
+    if (lk_pyramid > 0 && lk_pyramid <= 5) t->cfg.lk_pyramid_levels = lk_pyramid;
+    if (lk_iterations > 0) t->cfg.lk_iterations = lk_iterations;
+    if (lk_eps > 0.0) t->cfg.lk_eps = lk_eps;
+    if (f_edge_factor >= 0.0) t->cfg.f_threshold_edge_factor = f_edge_factor;
+    return VS_OK;
+}
+
+int vs_tracker_set_reject_callback(vs_tracker* t, vs_reject_fn fn, void* user) {
+    if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    t->reject_fn = fn;
+    t->reject_user = user;
+    return VS_OK;
+}
+
+int vs_tracker_reset(vs_tracker* t, int32_t stream) {
+    if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    if (stream < 0) {
+        VS_CUDA_TRY(cudaMemsetAsync(t->g.n, 0, sizeof(int) * t->B, t->stream));
+        t->has_prev = false;
+    } else {
+        if (stream >= t->B) { set_error("bad stream"); return VS_ERR_INVALID; }
+        VS_CUDA_TRY(cudaMemsetAsync(t->g.n + stream, 0, sizeof(int), t->stream));
+    }
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    return VS_OK;
+}
+
+int64_t vs_tracker_launch_count(const vs_tracker* t) { return t ? t->launches : 0; }
+float vs_tracker_last_device_ms(const vs_tracker* t) { return t ? t->last_ms : 0.f; }
+
+}  // extern "C"
+
+// =================================================================================================
+// stage entry points — the same kernels as the frame path, on stream slot 0 of the handle.
+// They use the handle's buffers as scratch, so tracking state is reset afterwards.
+// =================================================================================================
+namespace vs {
+
+static int stage_begin(vs_tracker* t) {
+    if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    sync_glue_params(t);
+    return upload_disc(t);
+}
+
+static int stage_end(vs_tracker* t) {
+    VS_CUDA_TRY(cudaMemsetAsync(t->g.n, 0, sizeof(int) * t->B, t->stream));
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    VS_CUDA_TRY(cudaGetLastError());
+    t->has_prev = false;
+    return VS_OK;
+}
+
+static int upload_level0(vs_tracker* t, int buf, const uint8_t* img) {
+    const LevelDesc& l0 = t->pd.lv[0];
+    VS_CUDA_TRY(cudaMemcpy2DAsync(t->d_pyr[buf] + l0.offset, l0.pitch, img, t->W, t->W, t->H, cudaMemcpyHostToDevice,
+                                  t->stream));
+    return VS_OK;
+}
+
+static EigParams make_eig_params(vs_tracker* t, int buf) {
+    EigParams e{};
+    e.img = t->d_pyr[buf] + t->pd.lv[0].offset;
+    e.pitch = t->pd.lv[0].pitch;
+    e.img_stride = t->pd.stream_bytes;
+    e.mask = t->g.mask;
+    e.mask_pitch = t->g.mask_pitch;
+    e.mask_stride = t->g.mask_stride;
+    e.W = t->W;
+    e.H = t->H;
+    e.want = t->g.want;
+    e.max_enc = t->g.max_enc;
+    e.cand = t->g.cand;
+    e.cand_count = t->g.cand_count;
+    e.cand_cap = t->g.cand_cap;
+    e.eig_out = nullptr;
+    e.quality = 0.01;
+    return e;
+}
+
+}  // namespace vs
+
+extern "C" {
+
+int vs_stage_clahe(vs_tracker* t, const uint8_t* img, uint8_t* out) {
+    int rc = stage_begin(t);
+    if (rc != VS_OK) return rc;
+    if (!img || !out) { set_error("null argument"); return VS_ERR_INVALID; }
+    const int nb = 1 - t->cur;
+    const LevelDesc& l0 = t->pd.lv[0];
+    VS_CUDA_TRY(cudaMemcpy2DAsync(t->d_raw, t->raw_pitch, img, t->W, t->W, t->H, cudaMemcpyHostToDevice, t->stream));
+    launch_clahe(t->d_raw, t->raw_pitch, t->raw_stride, t->d_pyr[nb] + l0.offset, l0.pitch, t->pd.stream_bytes, t->W,
+                 t->H, 1, t->d_luts, t->stream, &t->launches);
+    VS_CUDA_TRY(cudaMemcpy2DAsync(out, t->W, t->d_pyr[nb] + l0.offset, l0.pitch, t->W, t->H, cudaMemcpyDeviceToHost,
+                                  t->stream));
+    return stage_end(t);
+}
+
+int vs_stage_pyramid(vs_tracker* t, const uint8_t* level0, uint8_t* out_levels, int32_t* sizes, int32_t* n_levels) {
+    int rc = stage_begin(t);
+    if (rc != VS_OK) return rc;
+    if (!level0 || !out_levels || !sizes || !n_levels) { set_error("null argument"); return VS_ERR_INVALID; }
+    const int nb = 1 - t->cur;
+    rc = upload_level0(t, nb, level0);
+    if (rc != VS_OK) return rc;
+    const int nl = levels_to_build(t);
+    for (int l = 0; l + 1 < nl; ++l) launch_pyr_down(t->d_pyr[nb], t->pd, l, 1, t->stream, &t->launches);
+    size_t off = 0;
+    for (int l = 0; l < nl; ++l) {
+        const LevelDesc& L = t->pd.lv[l];
+        VS_CUDA_TRY(cudaMemcpy2DAsync(out_levels + off, L.w, t->d_pyr[nb] + L.offset, L.pitch, L.w, L.h,
+                                      cudaMemcpyDeviceToHost, t->stream));
+        off += (size_t)L.w * L.h;
+        sizes[2 * l] = L.w;
+        sizes[2 * l + 1] = L.h;
+    }
+    *n_levels = nl;
+    return stage_end(t);
+}
+
+int vs_stage_lk(vs_tracker* t, const uint8_t* prev_level0, const uint8_t* next_level0, const float* pts_xy, int32_t n,
+                float* next_xy, uint8_t* status) {
+    int rc = stage_begin(t);
+    if (rc != VS_OK) return rc;
+    if (!prev_level0 || !next_level0 || !pts_xy || !next_xy || !status || n < 0) { set_error("bad argument"); return VS_ERR_INVALID; }
+    if (n > t->cap) { set_error("n %d above capacity %d", n, t->cap); return VS_ERR_CAPACITY; }
+    const int nl = levels_to_build(t);
+    for (int b = 0; b < 2; ++b) {
+        rc = upload_level0(t, b, b == 0 ? prev_level0 : next_level0);
+        if (rc != VS_OK) return rc;
+        for (int l = 0; l + 1 < nl; ++l) launch_pyr_down(t->d_pyr[b], t->pd, l, 1, t->stream, &t->launches);
+        t->built[b] = nl;
+    }
+    VS_CUDA_TRY(cudaMemcpyAsync(t->g.pts, pts_xy, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->g.n, &n, sizeof(int), cudaMemcpyHostToDevice, t->stream));
+    LkParams p;
+    fill_lk_params(t, p, 0, 1, t->g.pts, t->g.lk_next, t->g.lk_status);
+    if (launch_lk(p, 1, n, t->stream, &t->launches) != 0) { set_error("LK: unsupported window"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaMemcpyAsync(next_xy, t->g.lk_next, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(status, t->g.lk_status, n, cudaMemcpyDeviceToHost, t->stream));
+    return stage_end(t);
+}
+
+static int stage_prepare_mask(vs_tracker* t, const float* kept_xy, int n_kept, int want) {
+    GlueParams g1 = t->g;
+    g1.n_streams = 1;
+    if (n_kept > 0) VS_CUDA_TRY(cudaMemcpyAsync(g1.k_pts, kept_xy, sizeof(float) * 2 * n_kept, cudaMemcpyHostToDevice, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(g1.kn, &n_kept, sizeof(int), cudaMemcpyHostToDevice, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(g1.want, &want, sizeof(int), cudaMemcpyHostToDevice, t->stream));
+    VS_CUDA_TRY(cudaMemsetAsync(g1.cand_count, 0, sizeof(int), t->stream));
+    VS_CUDA_TRY(cudaMemsetAsync(g1.max_enc, 0, sizeof(int), t->stream));
+    g1.max_cnt = n_kept > 0 ? n_kept : 1;
+    launch_paint_mask(g1, t->stream, &t->launches);
+    return VS_OK;
+}
+
+int vs_stage_min_eig(vs_tracker* t, const uint8_t* img, float* eig) {
+    int rc = stage_begin(t);
+    if (rc != VS_OK) return rc;
+    if (!img || !eig) { set_error("null argument"); return VS_ERR_INVALID; }
+    const int nb = 1 - t->cur;
+    rc = upload_level0(t, nb, img);
+    if (rc != VS_OK) return rc;
+    if (!t->d_eig) VS_CUDA_TRY(cudaMalloc(&t->d_eig, sizeof(float) * (size_t)t->W * t->H));
+    rc = stage_prepare_mask(t, nullptr, 0, 1);
+    if (rc != VS_OK) return rc;
+    EigParams e = make_eig_params(t, nb);
+    e.eig_out = t->d_eig;
+    launch_eig_max(e, 1, t->stream, &t->launches);
+    VS_CUDA_TRY(cudaMemcpyAsync(eig, t->d_eig, sizeof(float) * (size_t)t->W * t->H, cudaMemcpyDeviceToHost, t->stream));
+    return stage_end(t);
+}
+
+int vs_stage_good_features(vs_tracker* t, const uint8_t* img, const float* kept_xy, int32_t n_kept, int32_t max_corners,
+                           float* corners_xy, int32_t* n_out, uint8_t* mask_out) {
+    int rc = stage_begin(t);
+    if (rc != VS_OK) return rc;
+    if (!img || !corners_xy || !n_out || n_kept < 0 || (n_kept > 0 && !kept_xy)) { set_error("bad argument"); return VS_ERR_INVALID; }
+    if (n_kept + max_corners > t->cap) { set_error("n_kept + max_corners above capacity %d", t->cap); return VS_ERR_CAPACITY; }
+    const int nb = 1 - t->cur;
+    rc = upload_level0(t, nb, img);
+    if (rc != VS_OK) return rc;
+    rc = stage_prepare_mask(t, kept_xy, n_kept, max_corners);
+    if (rc != VS_OK) return rc;
+    EigParams e = make_eig_params(t, nb);
+    launch_eig_max(e, 1, t->stream, &t->launches);
+    launch_eig_candidates(e, 1, t->stream, &t->launches);
+    GlueParams g1 = t->g;
+    g1.n_streams = 1;
+    double zero = 0.0;
+    VS_CUDA_TRY(cudaMemcpyAsync(t->d_cur_time, &zero, sizeof(double), cudaMemcpyHostToDevice, t->stream));
+    launch_select_finish(g1, t->stream, &t->launches);
+    int hdr[kHdrInts];
+    VS_CUDA_TRY(cudaMemcpyAsync(hdr, g1.r_hdr, sizeof(hdr), cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    const int nn = hdr[H_NNEW];
+    *n_out = nn;
+    if (nn > 0) VS_CUDA_TRY(cudaMemcpyAsync(corners_xy, g1.r_pts + n_kept, sizeof(float) * 2 * nn, cudaMemcpyDeviceToHost, t->stream));
+    if (mask_out) VS_CUDA_TRY(cudaMemcpy2DAsync(mask_out, t->W, g1.mask, g1.mask_pitch, t->W, t->H, cudaMemcpyDeviceToHost, t->stream));
+    return stage_end(t);
+}
+
+int vs_stage_undistort(vs_tracker* t, const float* pts_xy, int32_t n, float* out_xy) {
+    int rc = stage_begin(t);
+    if (rc != VS_OK) return rc;
+    if (n < 0 || (n > 0 && (!pts_xy || !out_xy))) { set_error("bad argument"); return VS_ERR_INVALID; }
+    const int64_t room = (int64_t)t->B * t->cap;
+    for (int64_t off = 0; off < n; off += room) {
+        const int m = (int)((n - off) < room ? (n - off) : room);
+        VS_CUDA_TRY(cudaMemcpyAsync(t->g.w_cur, pts_xy + 2 * off, sizeof(float) * 2 * m, cudaMemcpyHostToDevice, t->stream));
+        launch_undistort(t->g.cam, t->g.w_cur, m, t->g.w_next, t->stream);
+        t->launches += 1;
+        VS_CUDA_TRY(cudaMemcpyAsync(out_xy + 2 * off, t->g.w_next, sizeof(float) * 2 * m, cudaMemcpyDeviceToHost, t->stream));
+        VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    }
+    return stage_end(t);
+}
+
+int vs_stage_set_mask(vs_tracker* t, const float* pts_xy, const int32_t* track_cnt, int32_t n, int32_t* keep_idx,
+                      int32_t* n_keep) {
+    int rc = stage_begin(t);
+    if (rc != VS_OK) return rc;
+    if (n < 0 || !n_keep || (n > 0 && (!pts_xy || !track_cnt || !keep_idx))) { set_error("bad argument"); return VS_ERR_INVALID; }
+    if (n > t->cap) { set_error("n above capacity"); return VS_ERR_CAPACITY; }
+    GlueParams g1 = t->g;
+    g1.n_streams = 1;
+    std::vector<int> idx(n);
+    for (int i = 0; i < n; ++i) idx[i] = i;
+    if (n > 0) {
+        VS_CUDA_TRY(cudaMemcpyAsync(g1.w_next, pts_xy, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, t->stream));
+        VS_CUDA_TRY(cudaMemcpyAsync(g1.w_cnt, track_cnt, sizeof(int) * n, cudaMemcpyHostToDevice, t->stream));
+        VS_CUDA_TRY(cudaMemcpyAsync(g1.w_ids, idx.data(), sizeof(int) * n, cudaMemcpyHostToDevice, t->stream));
+    }
+    VS_CUDA_TRY(cudaMemcpyAsync(g1.wn, &n, sizeof(int), cudaMemcpyHostToDevice, t->stream));
+    VS_CUDA_TRY(cudaMemsetAsync(g1.ransac_flag, 0, sizeof(int), t->stream));
+    launch_set_mask(g1, t->stream, &t->launches);
+    int kn = 0;
+    VS_CUDA_TRY(cudaMemcpyAsync(&kn, g1.kn, sizeof(int), cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    *n_keep = kn;
+    if (kn > 0) VS_CUDA_TRY(cudaMemcpyAsync(keep_idx, g1.k_ids, sizeof(int) * kn, cudaMemcpyDeviceToHost, t->stream));
+    return stage_end(t);
+}
+
+}  // extern "C"

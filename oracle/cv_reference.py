@@ -274,8 +274,9 @@ class RefFeatureTracker:
             for i in range(n):
                 if self.ids[i] != -1 and self.ids[i] in self.prev_undistorted_pts_map and dt > 1e-4:
                     px, py = self.prev_undistorted_pts_map[self.ids[i]]
-                    vel[i, 0] = np.float32((float(self.cur_undistorted_pts[i][0]) - float(px)) / dt)
-                    vel[i, 1] = np.float32((float(self.cur_undistorted_pts[i][1]) - float(py)) / dt)
+                    # float - float is a float32 subtraction in the reference, then / double dt
+                    vel[i, 0] = np.float32(float(np.float32(self.cur_undistorted_pts[i][0]) - np.float32(px)) / dt)
+                    vel[i, 1] = np.float32(float(np.float32(self.cur_undistorted_pts[i][1]) - np.float32(py)) / dt)
         self.pts_velocity = vel
         self.prev_undistorted_pts_map = dict(self.cur_undistorted_pts_map)
 

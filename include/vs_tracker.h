@@ -169,10 +169,19 @@ VS_API int vs_stage_set_mask(struct vs_tracker* t, const float* pts_xy, const in
                       int32_t* keep_idx, int32_t* n_keep);
 /* F-matrix RANSAC on virtual-pinhole points (device implementation) */
 VS_API int vs_stage_ransac(struct vs_tracker* t, const float* a_xy, const float* b_xy, int32_t n, uint8_t* status);
-/* repeat one dense stage `reps` times on device-resident synthetic data of all streams and return
- * the mean kernel time in ms (CUDA events); used by bench.py for per-kernel roofline numbers.
- * stage: 0 clahe_hist 1 clahe_apply 2 pyr_down(all levels) 3 lk 4 eig_max 5 eig_candidates */
-VS_API int vs_stage_time(struct vs_tracker* t, int32_t stage, int32_t reps, float* ms_out);
+/* ---- measurement hooks (bench.py) ---- */
+/* The handle's CUDA stream (a cudaStream_t): lets a caller record its own events on the stream the
+ * kernels are launched on, or order its own work after a track call. */
+VS_API void* vs_tracker_cuda_stream(const struct vs_tracker* t);
+/* Per-kernel CUDA-event timing of the frame path.  on != 0 brackets every kernel of each following
+ * track call with events on the handle's stream and accumulates the elapsed times (it adds a
+ * stream synchronise per call, so it is for profiling passes, not the timed throughput region);
+ * switching it on also clears the accumulators. */
+VS_API int vs_tracker_set_profiling(struct vs_tracker* t, int32_t on);
+/* total_ms[i] / launches[i] for kernel slot i < *n_out <= max_n; names from vs_profile_kernel_name */
+VS_API int vs_tracker_get_profile(const struct vs_tracker* t, int32_t max_n, float* total_ms, int32_t* launches,
+                                  int32_t* n_out);
+VS_API const char* vs_profile_kernel_name(int32_t slot);
 
 #ifdef __cplusplus
 }

@@ -57,7 +57,8 @@ EXPORTS = [
     "vs_tracker_set_reject_callback", "vs_tracker_reset", "vs_tracker_launch_count",
     "vs_tracker_last_device_ms", "vs_stage_clahe", "vs_stage_pyramid", "vs_stage_lk",
     "vs_stage_min_eig", "vs_stage_good_features", "vs_stage_undistort", "vs_stage_set_mask",
-    "vs_stage_ransac", "vs_stage_time",
+    "vs_stage_ransac", "vs_tracker_cuda_stream", "vs_tracker_set_profiling", "vs_tracker_get_profile",
+    "vs_profile_kernel_name",
 ]
 
 _lib = None
@@ -103,7 +104,12 @@ def load():
     lib.vs_stage_undistort.argtypes = [vp, vp, i32, vp]
     lib.vs_stage_set_mask.argtypes = [vp, vp, vp, i32, vp, C.POINTER(i32)]
     lib.vs_stage_ransac.argtypes = [vp, vp, vp, i32, vp]
-    lib.vs_stage_time.argtypes = [vp, i32, i32, C.POINTER(C.c_float)]
+    lib.vs_tracker_cuda_stream.argtypes = [vp]
+    lib.vs_tracker_cuda_stream.restype = vp
+    lib.vs_tracker_set_profiling.argtypes = [vp, i32]
+    lib.vs_tracker_get_profile.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(i32), C.POINTER(i32)]
+    lib.vs_profile_kernel_name.argtypes = [i32]
+    lib.vs_profile_kernel_name.restype = C.c_char_p
     _lib = lib
     return lib
 

@@ -1,8 +1,6 @@
 // F-matrix RANSAC on the device — placeholder until the 7-point kernel lands.
-#include "../../include/vs_tracker.h"
-#include "glue.cuh"
+#include "tracker_state.h"
 
-struct vs_tracker;
 namespace vs {
 int launch_ransac(vs_tracker*) {
     set_error("VS_RANSAC_DEVICE is not built yet: use VS_RANSAC_OFF or VS_RANSAC_CALLBACK");
@@ -12,9 +10,5 @@ int launch_ransac(vs_tracker*) {
 
 extern "C" int vs_stage_ransac(vs_tracker*, const float*, const float*, int32_t, uint8_t*) {
     vs::set_error("vs_stage_ransac: device RANSAC is not built yet");
-    return VS_ERR_STATE;
-}
-extern "C" int vs_stage_time(vs_tracker*, int32_t, int32_t, float*) {
-    vs::set_error("vs_stage_time: not built yet");
     return VS_ERR_STATE;
 }

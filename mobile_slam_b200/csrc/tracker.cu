@@ -8,8 +8,7 @@
 #include <new>
 #include <vector>
 
-#include "../../include/vs_tracker.h"
-#include "glue.cuh"
+#include "tracker_state.h"
 
 namespace vs {
 
@@ -42,71 +41,9 @@ static std::vector<int> circle_half_widths(int radius) {
 
 static inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
 
-struct DeviceArena {
-    std::vector<void*> blocks;
-    template <class T>
-    cudaError_t alloc(T** p, size_t count, bool zero = true) {
-        void* q = nullptr;
-        cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 256);
-        if (e != cudaSuccess) return e;
-        blocks.push_back(q);
-        if (zero) {
-            e = cudaMemset(q, 0, count * sizeof(T) + 256);
-            if (e != cudaSuccess) return e;
-        }
-        *p = reinterpret_cast<T*>(q);
-        return cudaSuccess;
-    }
-    void release() {
-        for (void* b : blocks) cudaFree(b);
-        blocks.clear();
-    }
-};
-
 }  // namespace vs
 
 using namespace vs;
-
-struct vs_tracker {
-    vs_tracker_config cfg{};
-    int B = 0, W = 0, H = 0, cap = 0;
-    int raw_pitch = 0;
-    int64_t raw_stride = 0;
-    PyrDesc pd{};                 // geometry of every possible level (kMaxLevels)
-    int built[2] = {0, 0};        // levels built in each pyramid buffer
-    int cur = 0;                  // index of the reference (previous-frame) pyramid
-    bool has_prev = false;
-    int n_bound = 0;              // upper bound of per-stream feature counts (LK grid size)
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    float last_ms = 0.f;
-    int64_t launches = 0;
-    DeviceArena arena;
-    uint8_t* d_raw = nullptr;
-    uint8_t* d_pyr[2] = {nullptr, nullptr};
-    uint8_t* d_luts = nullptr;
-    uint8_t* d_base_mask = nullptr;
-    int* d_disc_hw = nullptr;
-    double* d_cur_time = nullptr;
-    float* d_eig = nullptr;       // lazily allocated dense eig map (stage API only)
-    GlueParams g{};
-    // pinned host mirrors
-    uint8_t* h_block = nullptr;   // results: hdr | ids | cnt | pts | un | vel
-    size_t h_block_bytes = 0;
-    uint8_t* d_rblock = nullptr;
-    double* h_time = nullptr;
-    // RANSAC callback hop
-    vs_reject_fn reject_fn = nullptr;
-    void* reject_user = nullptr;
-    int* h_wn = nullptr;
-    int* h_flag = nullptr;
-    float2* h_lcur = nullptr;
-    float2* h_lnext = nullptr;
-    float2* h_wnext = nullptr;
-    uint8_t* h_rstatus = nullptr;
-    std::vector<int> disc_hw_host;
-    int disc_radius = -1;
-};
 
 namespace vs {
 
@@ -192,6 +129,53 @@ static void sync_glue_params(vs_tracker* t) {
     g.f_edge_factor = t->cfg.f_threshold_edge_factor;
     g.fb_check = t->cfg.fb_check;
     g.fb_threshold = (float)t->cfg.fb_threshold;
+}
+
+
+// ---- per-kernel CUDA-event profile (vs_tracker_set_profiling) ----
+static const char* const kProfNames[PK_COUNT] = {
+    "input_copy", "clahe_lut", "clahe_apply", "pyr_down", "lk", "lk_backward", "post_lk", "ransac",
+    "set_mask", "mask_paint", "eig_max", "eig_candidates", "select_finish"};
+
+static void prof_begin(vs_tracker* t) {
+    Profiler& p = t->prof;
+    if (!p.on) return;
+    p.used = 0;
+    p.slot.clear();
+    if (p.ev.empty()) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        p.ev.push_back(e);
+    }
+    cudaEventRecord(p.ev[0], t->stream);
+    p.used = 1;
+}
+
+// the kernels launched since the previous tick belong to `slot`
+static void prof_tick(vs_tracker* t, int slot) {
+    Profiler& p = t->prof;
+    if (!p.on) return;
+    if ((int)p.ev.size() <= p.used) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        p.ev.push_back(e);
+    }
+    cudaEventRecord(p.ev[p.used], t->stream);
+    p.slot.push_back(slot);
+    ++p.used;
+}
+
+static void prof_end(vs_tracker* t) {
+    Profiler& p = t->prof;
+    if (!p.on || p.used < 2) return;
+    cudaEventSynchronize(p.ev[p.used - 1]);
+    for (int i = 0; i + 1 < p.used; ++i) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, p.ev[i], p.ev[i + 1]) == cudaSuccess) {
+            p.total_ms[p.slot[i]] += ms;
+            p.launches[p.slot[i]] += 1;
+        }
+    }
 }
 
 }  // namespace vs
@@ -434,6 +418,7 @@ void vs_tracker_destroy(vs_tracker* t) {
     if (t->h_lnext) cudaFreeHost(t->h_lnext);
     if (t->h_wnext) cudaFreeHost(t->h_wnext);
     if (t->h_rstatus) cudaFreeHost(t->h_rstatus);
+    for (cudaEvent_t e : t->prof.ev) cudaEventDestroy(e);
     if (t->ev0) cudaEventDestroy(t->ev0);
     if (t->ev1) cudaEventDestroy(t->ev1);
     if (t->stream) cudaStreamDestroy(t->stream);
@@ -475,14 +460,21 @@ static void fill_lk_params(vs_tracker* t, LkParams& p, int prev_buf, int next_bu
 // build the pyramid of the new frame into buffer `buf` from a device image
 static int build_pyramid(vs_tracker* t, int buf, const uint8_t* d_img, int pitch, int64_t stride) {
     const LevelDesc& l0 = t->pd.lv[0];
-    if (t->cfg.equalize)
-        launch_clahe(d_img, pitch, stride, t->d_pyr[buf] + l0.offset, l0.pitch, t->pd.stream_bytes, t->W, t->H, t->B,
-                     t->d_luts, t->stream, &t->launches);
-    else
+    if (t->cfg.equalize) {
+        launch_clahe_lut_only(d_img, pitch, stride, t->W, t->H, t->B, t->d_luts, t->stream);
+        prof_tick(t, PK_CLAHE_LUT);
+        launch_clahe_apply_only(d_img, pitch, stride, t->d_pyr[buf] + l0.offset, l0.pitch, t->pd.stream_bytes, t->W,
+                                t->H, t->B, t->d_luts, t->stream);
+        prof_tick(t, PK_CLAHE_APPLY);
+        t->launches += 2;
+    } else {
         launch_copy_image(d_img, pitch, stride, t->d_pyr[buf] + l0.offset, l0.pitch, t->pd.stream_bytes, t->W, t->H,
                           t->B, t->stream, &t->launches);
+        prof_tick(t, PK_CLAHE_APPLY);
+    }
     const int nl = levels_to_build(t);
     for (int l = 0; l + 1 < nl; ++l) launch_pyr_down(t->d_pyr[buf], t->pd, l, t->B, t->stream, &t->launches);
+    prof_tick(t, PK_PYR_DOWN);
     t->built[buf] = nl;
     return VS_OK;
 }
@@ -526,13 +518,16 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
         LkParams p;
         fill_lk_params(t, p, t->cur, nb, g.pts, g.lk_next, g.lk_status);
         if (launch_lk(p, t->B, t->n_bound, t->stream, &t->launches) != 0) { set_error("LK: unsupported window"); return VS_ERR_INVALID; }
+        prof_tick(t, PK_LK);
         if (t->cfg.fb_check) {
             LkParams q;
             fill_lk_params(t, q, nb, t->cur, g.lk_next, g.lk_back, g.lk_back_status);
             launch_lk(q, t->B, t->n_bound, t->stream, &t->launches);
+            prof_tick(t, PK_LK_BACK);
         }
     }
     launch_post_lk(g, t->stream, &t->launches);
+    prof_tick(t, PK_POST_LK);
     if (t->cfg.ransac_mode == VS_RANSAC_CALLBACK) {
         const int rc = ransac_callback_hop(t);
         if (rc != VS_OK) return rc;
@@ -540,8 +535,11 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
         const int rc = launch_ransac(t);
         if (rc != VS_OK) return rc;
     }
+    prof_tick(t, PK_RANSAC);
     launch_set_mask(g, t->stream, &t->launches);
+    prof_tick(t, PK_SET_MASK);
     launch_paint_mask(g, t->stream, &t->launches);
+    prof_tick(t, PK_MASK_PAINT);
     EigParams e{};
     e.img = t->d_pyr[nb] + t->pd.lv[0].offset;
     e.pitch = t->pd.lv[0].pitch;
@@ -559,8 +557,11 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
     e.eig_out = nullptr;
     e.quality = 0.01;
     launch_eig_max(e, t->B, t->stream, &t->launches);
+    prof_tick(t, PK_EIG_MAX);
     launch_eig_candidates(e, t->B, t->stream, &t->launches);
+    prof_tick(t, PK_EIG_CAND);
     launch_select_finish(g, t->stream, &t->launches);
+    prof_tick(t, PK_SELECT_FINISH);
     t->cur = nb;
     t->has_prev = true;
     VS_CUDA_TRY(cudaGetLastError());
@@ -619,6 +620,7 @@ int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_
     VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
     memcpy(t->h_time, time_s, sizeof(double) * t->B);
     VS_CUDA_TRY(cudaEventRecord(t->ev0, t->stream));
+    prof_begin(t);
     VS_CUDA_TRY(cudaMemcpyAsync(t->d_cur_time, t->h_time, sizeof(double) * t->B, cudaMemcpyHostToDevice, t->stream));
     const uint8_t* img = d_frames;
     int pitch = stride;
@@ -631,9 +633,11 @@ int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_
         pitch = t->raw_pitch;
         istride = t->raw_stride;
     }
+    prof_tick(t, PK_INPUT);
     const int rc = run_frame(t, img, pitch, istride);
     if (rc != VS_OK) return rc;
     VS_CUDA_TRY(cudaEventRecord(t->ev1, t->stream));
+    prof_end(t);
     if (results_to_host && out) {
         const int rc2 = vs_tracker_fetch_results(t, out);
         if (rc2 != VS_OK) return rc2;
@@ -707,6 +711,25 @@ int vs_tracker_reset(vs_tracker* t, int32_t stream) {
 }
 
 int64_t vs_tracker_launch_count(const vs_tracker* t) { return t ? t->launches : 0; }
+void* vs_tracker_cuda_stream(const vs_tracker* t) { return t ? (void*)t->stream : nullptr; }
+
+int vs_tracker_set_profiling(vs_tracker* t, int32_t on) {
+    if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    t->prof.on = on != 0;
+    if (on)
+        for (int i = 0; i < PK_COUNT; ++i) { t->prof.total_ms[i] = 0.0; t->prof.launches[i] = 0; }
+    return VS_OK;
+}
+
+int vs_tracker_get_profile(const vs_tracker* t, int32_t max_n, float* total_ms, int32_t* launches, int32_t* n_out) {
+    if (!t || !total_ms || !launches || !n_out) { set_error("null argument"); return VS_ERR_INVALID; }
+    const int n = max_n < PK_COUNT ? max_n : (int)PK_COUNT;
+    for (int i = 0; i < n; ++i) { total_ms[i] = (float)t->prof.total_ms[i]; launches[i] = t->prof.launches[i]; }
+    *n_out = n;
+    return VS_OK;
+}
+
+const char* vs_profile_kernel_name(int32_t slot) { return (slot >= 0 && slot < PK_COUNT) ? kProfNames[slot] : ""; }
 float vs_tracker_last_device_ms(const vs_tracker* t) { return t ? t->last_ms : 0.f; }
 
 }  // extern "C"

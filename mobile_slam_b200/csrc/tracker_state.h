@@ -1,0 +1,87 @@
+// Handle state of the C ABI (include/vs_tracker.h) shared by tracker.cu and ransac.cu.
+#pragma once
+#include <vector>
+
+#include "../../include/vs_tracker.h"
+#include "glue.cuh"
+
+namespace vs {
+
+// kernel slots of the per-kernel CUDA-event profile (vs_tracker_get_profile)
+enum ProfSlot { PK_INPUT = 0, PK_CLAHE_LUT, PK_CLAHE_APPLY, PK_PYR_DOWN, PK_LK, PK_LK_BACK, PK_POST_LK, PK_RANSAC,
+                PK_SET_MASK, PK_MASK_PAINT, PK_EIG_MAX, PK_EIG_CAND, PK_SELECT_FINISH, PK_COUNT };
+
+struct Profiler {
+    bool on = false;
+    std::vector<cudaEvent_t> ev;      // event pool, grown on demand
+    std::vector<int> slot;            // slot[i] = kernel that ran between ev[i] and ev[i+1]
+    int used = 0;
+    double total_ms[PK_COUNT] = {};
+    int launches[PK_COUNT] = {};
+};
+
+struct DeviceArena {
+    std::vector<void*> blocks;
+    template <class T>
+    cudaError_t alloc(T** p, size_t count, bool zero = true) {
+        void* q = nullptr;
+        cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 256);
+        if (e != cudaSuccess) return e;
+        blocks.push_back(q);
+        if (zero) {
+            e = cudaMemset(q, 0, count * sizeof(T) + 256);
+            if (e != cudaSuccess) return e;
+        }
+        *p = reinterpret_cast<T*>(q);
+        return cudaSuccess;
+    }
+    void release() {
+        for (void* b : blocks) cudaFree(b);
+        blocks.clear();
+    }
+};
+
+}  // namespace vs
+
+struct vs_tracker {
+    vs_tracker_config cfg{};
+    int B = 0, W = 0, H = 0, cap = 0;
+    int raw_pitch = 0;
+    int64_t raw_stride = 0;
+    vs::PyrDesc pd{};                 // geometry of every possible level (kMaxLevels)
+    int built[2] = {0, 0};        // levels built in each pyramid buffer
+    int cur = 0;                  // index of the reference (previous-frame) pyramid
+    bool has_prev = false;
+    int n_bound = 0;              // upper bound of per-stream feature counts (LK grid size)
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+    int64_t launches = 0;
+    vs::DeviceArena arena;
+    uint8_t* d_raw = nullptr;
+    uint8_t* d_pyr[2] = {nullptr, nullptr};
+    uint8_t* d_luts = nullptr;
+    uint8_t* d_base_mask = nullptr;
+    int* d_disc_hw = nullptr;
+    double* d_cur_time = nullptr;
+    float* d_eig = nullptr;       // lazily allocated dense eig map (stage API only)
+    vs::GlueParams g{};
+    // pinned host mirrors
+    uint8_t* h_block = nullptr;   // results: hdr | ids | cnt | pts | un | vel
+    size_t h_block_bytes = 0;
+    uint8_t* d_rblock = nullptr;
+    double* h_time = nullptr;
+    // RANSAC callback hop
+    vs_reject_fn reject_fn = nullptr;
+    void* reject_user = nullptr;
+    int* h_wn = nullptr;
+    int* h_flag = nullptr;
+    float2* h_lcur = nullptr;
+    float2* h_lnext = nullptr;
+    float2* h_wnext = nullptr;
+    uint8_t* h_rstatus = nullptr;
+    std::vector<int> disc_hw_host;
+    int disc_radius = -1;
+    vs::Profiler prof;
+};
+

@@ -298,10 +298,22 @@ class BatchTracker:
         _abi.check(self._lib.vs_stage_ransac(self._h, a.ctypes.data, b.ctypes.data, len(a), st.ctypes.data))
         return st
 
-    def stage_time(self, stage: int, reps: int = 20) -> float:
-        ms = C.c_float(0)
-        _abi.check(self._lib.vs_stage_time(self._h, stage, reps, C.byref(ms)))
-        return float(ms.value)
+    # ---- measurement hooks -------------------------------------------------------------------
+    @property
+    def cuda_stream(self) -> int:
+        """cudaStream_t of the handle (wrap with torch.cuda.ExternalStream to record events on it)."""
+        return int(self._lib.vs_tracker_cuda_stream(self._h) or 0)
+
+    def set_profiling(self, on: bool):
+        _abi.check(self._lib.vs_tracker_set_profiling(self._h, 1 if on else 0))
+
+    def profile(self) -> dict:
+        """{kernel name: (total_ms, launches)} accumulated since set_profiling(True)."""
+        ms = (C.c_float * 32)()
+        cnt = (C.c_int32 * 32)()
+        n = C.c_int32(0)
+        _abi.check(self._lib.vs_tracker_get_profile(self._h, 32, ms, cnt, C.byref(n)))
+        return {self._lib.vs_profile_kernel_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n.value)}
 
 
 class FeatureTracker:

@@ -200,36 +200,19 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// mask image: base (fisheye disc / file mask / 255) minus a filled circle of radius min_dist per kept point
+// K7: second half of cv::goodFeaturesToTrack — threshold 0.01 * max, order (eig desc, address desc),
+// greedy min-distance accept until `want` corners — then the rest of the frame: addPoints, updateID,
+// undistortedPoints + velocity (feature_tracker.cpp:89-95, 309-316, 338-380).
+//
+// The greedy consumes candidates in descending key order and stops at `want`, so only a prefix of the
+// order is ever looked at.  A 1024-bin histogram over the key range (threshold, max] finds the bin
+// boundary above which the M = max(64, 4*want) best keys live; only those are sorted (bitonic, shared
+// memory) and fed to the greedy.  If fewer than `want` are accepted the prefix is widened 4x and the
+// selection repeated, so the result always equals a full sort + greedy.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) fill_mask_kernel(GlueParams g) {
-    const int s = blockIdx.y;
-    if (g.want[s] <= 0) return;
-    const int64_t n16 = ((int64_t)g.H * g.mask_pitch) >> 4;
-    const uint4* b = reinterpret_cast<const uint4*>(g.base_mask);
-    uint4* m = reinterpret_cast<uint4*>(g.mask + (int64_t)s * g.mask_stride);
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (int64_t)gridDim.x * 256) m[i] = b[i];
-}
-
-__global__ void __launch_bounds__(64) paint_mask_kernel(GlueParams g) {
-    const int s = blockIdx.y, j = blockIdx.x;
-    if (g.want[s] <= 0 || j >= g.kn[s]) return;
-    const float2 p = g.k_pts[(int64_t)s * g.cap + j];
-    const int cx = cv_round(p.x), cy = cv_round(p.y), R = g.min_dist, D = 2 * R + 1;
-    uint8_t* m = g.mask + (int64_t)s * g.mask_stride;
-    for (int idx = threadIdx.x; idx < D * D; idx += 64) {
-        const int ry = idx / D, rx = idx - ry * D;
-        const int dy = ry - R, dx = rx - R;
-        const int y = cy + dy, x = cx + dx;
-        if (y >= 0 && y < g.H && x >= 0 && x < g.W && abs(dx) <= g.disc_hw[abs(dy)]) m[(int64_t)y * g.mask_pitch + x] = 0;
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// K7: sort candidates (eig desc, address desc), greedy min-distance accept, then finish the frame
-// ---------------------------------------------------------------------------------------------
-constexpr int kSortSmemKeys = 8192;
-constexpr int kFinishThreads = 1024;
+constexpr int kSortSmemKeys = 4096;
+constexpr int kFinishThreads = 256;
+constexpr int kSelBins = 1024;
 
 __device__ __forceinline__ void bitonic_sort_desc(unsigned long long* v, int N, int tid, int nthreads) {
     for (int k = 2; k <= N; k <<= 1) {
@@ -249,11 +232,48 @@ __device__ __forceinline__ void bitonic_sort_desc(unsigned long long* v, int N, 
     }
 }
 
+// greedy min-distance accept over keys sorted descending; returns the number accepted (<= want)
+__device__ __forceinline__ int greedy_accept(const unsigned long long* v, int nv, int want, int W, int md2, short2* newp,
+                                             int lane) {
+    int A = 0;
+    for (int q0 = 0; q0 < nv && A < want; q0 += 32) {
+        const int q = q0 + lane;
+        bool alive = q < nv;
+        int x = 0, y = 0;
+        if (alive) {
+            const unsigned int lin = (unsigned int)(v[q] & 0xffffffffull);
+            y = lin / W;
+            x = lin - y * W;
+            for (int a = 0; a < A && alive; ++a) {
+                const int dx = x - (int)newp[a].x, dy = y - (int)newp[a].y;
+                if (dx * dx + dy * dy < md2) alive = false;
+            }
+        }
+        unsigned int m = __ballot_sync(0xffffffffu, alive);
+        while (m && A < want) {
+            const int l = __ffs(m) - 1;
+            const int ax = __shfl_sync(0xffffffffu, x, l), ay = __shfl_sync(0xffffffffu, y, l);
+            if (lane == l) {
+                newp[A] = make_short2((short)x, (short)y);
+                alive = false;
+            } else if (alive && lane > l) {
+                const int dx = x - ax, dy = y - ay;
+                if (dx * dx + dy * dy < md2) alive = false;
+            }
+            ++A;
+            m = __ballot_sync(0xffffffffu, alive);
+        }
+        __syncwarp();
+    }
+    return A;
+}
+
 __global__ void __launch_bounds__(kFinishThreads) select_finish_kernel(GlueParams g) {
     extern __shared__ __align__(16) uint8_t dsm[];
     unsigned long long* skeys = reinterpret_cast<unsigned long long*>(dsm);       // [kSortSmemKeys]
-    short2* newp = reinterpret_cast<short2*>(skeys + kSortSmemKeys);               // [cap]
-    __shared__ int s_nnew;
+    int* hist = reinterpret_cast<int*>(skeys + kSortSmemKeys);                     // [kSelBins]
+    short2* newp = reinterpret_cast<short2*>(hist + kSelBins);                     // [cap]
+    __shared__ int s_nnew, s_cnt, s_bin, s_total;
     const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
     const int64_t o = (int64_t)s * g.cap;
     const int kn = g.kn[s];
@@ -267,53 +287,78 @@ __global__ void __launch_bounds__(kFinishThreads) select_finish_kernel(GlueParam
     }
     __syncthreads();
     if (nc > 0) {
-        int N = 1;
-        while (N < nc) N <<= 1;
         unsigned long long* gk = g.cand + (int64_t)s * g.cand_cap;
-        unsigned long long* v;
-        if (N <= kSortSmemKeys) {
-            for (int i = tid; i < N; i += kFinishThreads) skeys[i] = i < nc ? gk[i] : 0ull;
-            v = skeys;
-        } else {
-            for (int i = nc + tid; i < N; i += kFinishThreads) gk[i] = 0ull;
-            v = gk;
-        }
+        const unsigned int me = g.max_enc[s];
+        const float max_val = me ? float_order_dec(me) : 0.f;       // minMaxLoc on an empty mask gives 0
+        const float thr = (float)((double)max_val * 0.01);          // qualityLevel 0.01
+        // keys are (float bits << 32 | address); eig > thr >= 0, so the float bits order like integers
+        const unsigned int tb = __float_as_uint(thr > 0.f ? thr : 0.f);
+        const unsigned int mb = __float_as_uint(max_val > 0.f ? max_val : 0.f);
+        int shift = 0;
+        while (mb > tb && ((mb - tb) >> shift) >= (unsigned)kSelBins) ++shift;
+        for (int i = tid; i < kSelBins; i += kFinishThreads) hist[i] = 0;
+        if (tid == 0) s_total = 0;
         __syncthreads();
-        bitonic_sort_desc(v, N, tid, kFinishThreads);
-        if (tid < 32) {
-            const int W = g.W;
-            const int md2 = g.min_dist * g.min_dist;
-            int A = 0;
-            for (int q0 = 0; q0 < nc && A < want; q0 += 32) {
-                const int q = q0 + lane;
-                bool alive = q < nc;
-                int x = 0, y = 0;
-                if (alive) {
-                    const unsigned int lin = (unsigned int)(v[q] & 0xffffffffull);
-                    y = lin / W;
-                    x = lin - y * W;
-                    for (int a = 0; a < A && alive; ++a) {
-                        const int dx = x - (int)newp[a].x, dy = y - (int)newp[a].y;
-                        if (dx * dx + dy * dy < md2) alive = false;
-                    }
-                }
-                unsigned int m = __ballot_sync(0xffffffffu, alive);
-                while (m && A < want) {
-                    const int l = __ffs(m) - 1;
-                    const int ax = __shfl_sync(0xffffffffu, x, l), ay = __shfl_sync(0xffffffffu, y, l);
-                    if (lane == l) {
-                        newp[A] = make_short2((short)x, (short)y);
-                        alive = false;
-                    } else if (alive && lane > l) {
-                        const int dx = x - ax, dy = y - ay;
-                        if (dx * dx + dy * dy < md2) alive = false;
-                    }
-                    ++A;
-                    m = __ballot_sync(0xffffffffu, alive);
-                }
-                __syncwarp();
+        int mine = 0;
+        for (int i = tid; i < nc; i += kFinishThreads) {
+            const unsigned int eb = (unsigned int)(gk[i] >> 32);
+            if (__uint_as_float(eb) > thr) {
+                atomicAdd(&hist[min((eb - tb) >> shift, (unsigned)kSelBins - 1)], 1);
+                ++mine;
             }
-            if (lane == 0) s_nnew = A;
+        }
+        if (mine) atomicAdd(&s_total, mine);
+        __syncthreads();
+        const int n_valid = s_total;
+        const int md2 = g.min_dist * g.min_dist;
+        int target = max(64, 4 * want);
+        while (n_valid > 0) {
+            __syncthreads();
+            // highest bin boundary b such that bins >= b hold at least `target` keys (or everything)
+            if (tid == 0) {
+                int acc = 0, b = kSelBins - 1;
+                for (; b > 0; --b) {
+                    acc += hist[b];
+                    if (acc >= target) break;
+                }
+                if (b == 0) acc += hist[0];
+                s_bin = b;
+                s_cnt = 0;
+                s_total = acc;
+            }
+            __syncthreads();
+            const int bsel = s_bin, nsel = s_total;
+            const bool all = nsel >= n_valid;
+            unsigned long long* v;
+            int N = 1;
+            while (N < nsel) N <<= 1;
+            if (N <= kSortSmemKeys) {
+                v = skeys;
+                for (int i = tid; i < nc; i += kFinishThreads) {
+                    const unsigned long long key = gk[i];
+                    const unsigned int eb = (unsigned int)(key >> 32);
+                    if (__uint_as_float(eb) > thr && (int)min((eb - tb) >> shift, (unsigned)kSelBins - 1) >= bsel)
+                        skeys[atomicAdd(&s_cnt, 1)] = key;
+                }
+                for (int i = nsel + tid; i < N; i += kFinishThreads) skeys[i] = 0ull;
+            } else {
+                // too many for shared memory (first frames of feature-heavy configs): sort the whole list in place
+                N = 1;
+                while (N < nc) N <<= 1;
+                for (int i = tid; i < N; i += kFinishThreads)
+                    if (i >= nc || !(__uint_as_float((unsigned int)(gk[i] >> 32)) > thr)) gk[i] = 0ull;
+                v = gk;
+            }
+            __syncthreads();
+            bitonic_sort_desc(v, N, tid, kFinishThreads);
+            const int nv = (v == gk) ? n_valid : nsel;
+            if (tid < 32) {
+                const int A = greedy_accept(v, nv, want, g.W, md2, newp, lane);
+                if (lane == 0) s_nnew = A;
+            }
+            __syncthreads();
+            if (s_nnew >= want || all || v == gk) break;
+            target *= 4;
         }
     }
     __syncthreads();
@@ -390,17 +435,8 @@ void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches) {
     if (launches) *launches += 1;
 }
 
-void launch_paint_mask(const GlueParams& g, cudaStream_t st, int64_t* launches) {
-    const int64_t n16 = ((int64_t)g.H * g.mask_pitch) >> 4;
-    int blocks = (int)((n16 + 255) / 256);
-    if (blocks > 64) blocks = 64;
-    fill_mask_kernel<<<dim3(blocks, g.n_streams), 256, 0, st>>>(g);
-    paint_mask_kernel<<<dim3(g.max_cnt, g.n_streams), 64, 0, st>>>(g);
-    if (launches) *launches += 2;
-}
-
 void launch_select_finish(const GlueParams& g, cudaStream_t st, int64_t* launches) {
-    const int smem = kSortSmemKeys * 8 + g.cap * 4;
+    const int smem = kSortSmemKeys * 8 + kSelBins * 4 + g.cap * 4;
     static int configured = 0;
     if (configured < smem) {
         cudaFuncSetAttribute(select_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);

@@ -41,24 +41,35 @@ struct LkParams {
 int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches);
 
 // ---- shitomasi.cu (K5, K6) ----
-struct EigParams {
+struct StParams {
     const uint8_t* img;       // level 0 of the new pyramid
-    int pitch;
-    int64_t img_stride;
-    const uint8_t* mask;      // [n_streams][H][mask_pitch]
-    int mask_pitch;
-    int64_t mask_stride;
+    int pitch;                // bytes, multiple of 16
+    int64_t img_stride;       // bytes between two streams' images
     int W, H;
+    int nx, ny, words_per_strip, rows_per_strip;   // strip grid (filled by launch_shi_tomasi)
     const int* want;          // [n_streams] corners wanted; streams with want <= 0 are skipped (may be null)
+    // analytic mask = base minus the min_dist discs of the kept features
+    const int* kn;            // [n_streams] kept features (may be null = none)
+    const float2* k_pts;      // [n_streams][cap]
+    int cap;
+    int min_dist;
+    const int* disc_hw;       // [min_dist + 1] cv::circle row half widths
+    int base_mode;            // 0 all pixels, 1 auto fisheye circle, 2 mask image
+    int fcx, fcy, fr;         // fisheye circle (feature_tracker.cpp:50-58)
+    const int* fish_hw;       // [fr + 1]
+    const uint8_t* base_mask; // [H][mask_pitch] (base_mode 2)
+    int mask_pitch;
     unsigned int* max_enc;    // [n_streams] order-preserving encoding of the masked max
     unsigned long long* cand; // [n_streams][cand_cap] (eig bits << 32 | y*W + x)
     int* cand_count;          // [n_streams]
     int cand_cap;
     float* eig_out;           // optional dense eig map [n_streams][H][W] (stage tests), else null
+    uint8_t* mask_out;        // optional mask image [n_streams][H][mask_out_pitch] (stage tests), else null
+    int mask_out_pitch;
+    int64_t mask_out_stride;
     double quality;           // 0.01
 };
-void launch_eig_max(const EigParams& p, int n_streams, cudaStream_t st, int64_t* launches);
-void launch_eig_candidates(const EigParams& p, int n_streams, cudaStream_t st, int64_t* launches);
+void launch_shi_tomasi(const StParams& p, int n_streams, cudaStream_t st, int64_t* launches);
 
 __host__ __device__ inline unsigned int float_order_enc(float f) {
 #ifdef __CUDA_ARCH__

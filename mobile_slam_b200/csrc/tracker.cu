@@ -135,7 +135,7 @@ static void sync_glue_params(vs_tracker* t) {
 // ---- per-kernel CUDA-event profile (vs_tracker_set_profiling) ----
 static const char* const kProfNames[PK_COUNT] = {
     "input_copy", "clahe_lut", "clahe_apply", "pyr_down", "lk", "lk_backward", "post_lk", "ransac",
-    "set_mask", "mask_paint", "eig_max", "eig_candidates", "select_finish"};
+    "set_mask", "shi_tomasi", "select_finish"};
 
 static void prof_begin(vs_tracker* t) {
     Profiler& p = t->prof;
@@ -300,6 +300,7 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     VS_TRY_CREATE(A.alloc(&t->d_pyr[1], (size_t)(B * t->pd.stream_bytes)));
     VS_TRY_CREATE(A.alloc(&t->d_luts, (size_t)(B * 64 * 256)));
     VS_TRY_CREATE(A.alloc(&t->d_disc_hw, (size_t)kMaxDiscRadius + 1));
+    VS_TRY_CREATE(A.alloc(&t->d_fish_hw, (size_t)(t->W > t->H ? t->W : t->H) + 2));
     VS_TRY_CREATE(A.alloc(&t->d_cur_time, (size_t)B));
     g.cur_time = t->d_cur_time;
     VS_TRY_CREATE(A.alloc(&g.n, B));
@@ -331,7 +332,7 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     VS_TRY_CREATE(A.alloc(&g.want, B));
     g.mask_pitch = round_up(t->W, 16);
     g.mask_stride = (int64_t)round_up(g.mask_pitch * t->H, 256);
-    VS_TRY_CREATE(A.alloc(&g.mask, (size_t)(B * g.mask_stride)));
+    VS_TRY_CREATE(A.alloc(&g.mask, (size_t)g.mask_stride));     // stage API only: the frame path never materialises a mask
     VS_TRY_CREATE(A.alloc(&t->d_base_mask, (size_t)g.mask_stride));
     g.base_mask = t->d_base_mask;
     g.disc_hw = t->d_disc_hw;
@@ -370,6 +371,7 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
         if (cfg->fisheye && cfg->fisheye_mask_image) {
             const int st = cfg->fisheye_mask_stride > 0 ? cfg->fisheye_mask_stride : W;
             for (int y = 0; y < H; ++y) memcpy(&m[(size_t)y * mp], cfg->fisheye_mask_image + (size_t)y * st, W);
+            t->base_mode = 2;
         } else if (cfg->fisheye) {
             const double cx = W / 2.0, cy = H / 2.0;
             double rad = cx;
@@ -379,6 +381,11 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
             rad *= 0.95;
             const int icx = (int)cx, icy = (int)cy, r = (int)rad;
             const std::vector<int> hw = circle_half_widths(r);
+            t->base_mode = 1;
+            t->fcx = icx;
+            t->fcy = icy;
+            t->fr = r;
+            VS_TRY_CREATE(cudaMemcpy(t->d_fish_hw, hw.data(), sizeof(int) * (r + 1), cudaMemcpyHostToDevice));
             for (int dy = -r; dy <= r; ++dy) {
                 const int y = icy + dy, w = hw[dy < 0 ? -dy : dy];
                 if (y < 0 || y >= H || w < 0) continue;
@@ -506,6 +513,37 @@ static int ransac_callback_hop(vs_tracker* t) {
     return VS_OK;
 }
 
+// Shi-Tomasi launch parameters: image = level 0 of pyramid buffer `buf`, mask discs = g's kept set
+static StParams make_st_params(vs_tracker* t, int buf, const GlueParams& g) {
+    StParams e{};
+    e.img = t->d_pyr[buf] + t->pd.lv[0].offset;
+    e.pitch = t->pd.lv[0].pitch;
+    e.img_stride = t->pd.stream_bytes;
+    e.W = t->W;
+    e.H = t->H;
+    e.want = g.want;
+    e.kn = g.kn;
+    e.k_pts = g.k_pts;
+    e.cap = g.cap;
+    e.min_dist = g.min_dist;
+    e.disc_hw = g.disc_hw;
+    e.base_mode = t->base_mode;
+    e.fcx = t->fcx;
+    e.fcy = t->fcy;
+    e.fr = t->fr;
+    e.fish_hw = t->d_fish_hw;
+    e.base_mask = g.base_mask;
+    e.mask_pitch = g.mask_pitch;
+    e.max_enc = g.max_enc;
+    e.cand = g.cand;
+    e.cand_count = g.cand_count;
+    e.cand_cap = g.cand_cap;
+    e.eig_out = nullptr;
+    e.mask_out = nullptr;
+    e.quality = 0.01;
+    return e;
+}
+
 static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t stride) {
     GlueParams& g = t->g;
     sync_glue_params(t);
@@ -538,28 +576,9 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
     prof_tick(t, PK_RANSAC);
     launch_set_mask(g, t->stream, &t->launches);
     prof_tick(t, PK_SET_MASK);
-    launch_paint_mask(g, t->stream, &t->launches);
-    prof_tick(t, PK_MASK_PAINT);
-    EigParams e{};
-    e.img = t->d_pyr[nb] + t->pd.lv[0].offset;
-    e.pitch = t->pd.lv[0].pitch;
-    e.img_stride = t->pd.stream_bytes;
-    e.mask = g.mask;
-    e.mask_pitch = g.mask_pitch;
-    e.mask_stride = g.mask_stride;
-    e.W = t->W;
-    e.H = t->H;
-    e.want = g.want;
-    e.max_enc = g.max_enc;
-    e.cand = g.cand;
-    e.cand_count = g.cand_count;
-    e.cand_cap = g.cand_cap;
-    e.eig_out = nullptr;
-    e.quality = 0.01;
-    launch_eig_max(e, t->B, t->stream, &t->launches);
-    prof_tick(t, PK_EIG_MAX);
-    launch_eig_candidates(e, t->B, t->stream, &t->launches);
-    prof_tick(t, PK_EIG_CAND);
+    StParams e = make_st_params(t, nb, g);
+    launch_shi_tomasi(e, t->B, t->stream, &t->launches);
+    prof_tick(t, PK_SHI_TOMASI);
     launch_select_finish(g, t->stream, &t->launches);
     prof_tick(t, PK_SELECT_FINISH);
     t->cur = nb;
@@ -762,26 +781,6 @@ static int upload_level0(vs_tracker* t, int buf, const uint8_t* img) {
     return VS_OK;
 }
 
-static EigParams make_eig_params(vs_tracker* t, int buf) {
-    EigParams e{};
-    e.img = t->d_pyr[buf] + t->pd.lv[0].offset;
-    e.pitch = t->pd.lv[0].pitch;
-    e.img_stride = t->pd.stream_bytes;
-    e.mask = t->g.mask;
-    e.mask_pitch = t->g.mask_pitch;
-    e.mask_stride = t->g.mask_stride;
-    e.W = t->W;
-    e.H = t->H;
-    e.want = t->g.want;
-    e.max_enc = t->g.max_enc;
-    e.cand = t->g.cand;
-    e.cand_count = t->g.cand_count;
-    e.cand_cap = t->g.cand_cap;
-    e.eig_out = nullptr;
-    e.quality = 0.01;
-    return e;
-}
-
 }  // namespace vs
 
 extern "C" {
@@ -853,8 +852,6 @@ static int stage_prepare_mask(vs_tracker* t, const float* kept_xy, int n_kept, i
     VS_CUDA_TRY(cudaMemcpyAsync(g1.want, &want, sizeof(int), cudaMemcpyHostToDevice, t->stream));
     VS_CUDA_TRY(cudaMemsetAsync(g1.cand_count, 0, sizeof(int), t->stream));
     VS_CUDA_TRY(cudaMemsetAsync(g1.max_enc, 0, sizeof(int), t->stream));
-    g1.max_cnt = n_kept > 0 ? n_kept : 1;
-    launch_paint_mask(g1, t->stream, &t->launches);
     return VS_OK;
 }
 
@@ -868,9 +865,9 @@ int vs_stage_min_eig(vs_tracker* t, const uint8_t* img, float* eig) {
     if (!t->d_eig) VS_CUDA_TRY(cudaMalloc(&t->d_eig, sizeof(float) * (size_t)t->W * t->H));
     rc = stage_prepare_mask(t, nullptr, 0, 1);
     if (rc != VS_OK) return rc;
-    EigParams e = make_eig_params(t, nb);
+    StParams e = make_st_params(t, nb, t->g);
     e.eig_out = t->d_eig;
-    launch_eig_max(e, 1, t->stream, &t->launches);
+    launch_shi_tomasi(e, 1, t->stream, &t->launches);
     VS_CUDA_TRY(cudaMemcpyAsync(eig, t->d_eig, sizeof(float) * (size_t)t->W * t->H, cudaMemcpyDeviceToHost, t->stream));
     return stage_end(t);
 }
@@ -886,9 +883,14 @@ int vs_stage_good_features(vs_tracker* t, const uint8_t* img, const float* kept_
     if (rc != VS_OK) return rc;
     rc = stage_prepare_mask(t, kept_xy, n_kept, max_corners);
     if (rc != VS_OK) return rc;
-    EigParams e = make_eig_params(t, nb);
-    launch_eig_max(e, 1, t->stream, &t->launches);
-    launch_eig_candidates(e, 1, t->stream, &t->launches);
+    StParams e = make_st_params(t, nb, t->g);
+    if (mask_out) {
+        e.mask_out = t->g.mask;
+        e.mask_out_pitch = t->g.mask_pitch;
+        e.mask_out_stride = t->g.mask_stride;
+        VS_CUDA_TRY(cudaMemsetAsync(t->g.mask, 0, (size_t)t->g.mask_stride, t->stream));
+    }
+    launch_shi_tomasi(e, 1, t->stream, &t->launches);
     GlueParams g1 = t->g;
     g1.n_streams = 1;
     double zero = 0.0;

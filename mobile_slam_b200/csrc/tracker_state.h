@@ -9,7 +9,7 @@ namespace vs {
 
 // kernel slots of the per-kernel CUDA-event profile (vs_tracker_get_profile)
 enum ProfSlot { PK_INPUT = 0, PK_CLAHE_LUT, PK_CLAHE_APPLY, PK_PYR_DOWN, PK_LK, PK_LK_BACK, PK_POST_LK, PK_RANSAC,
-                PK_SET_MASK, PK_MASK_PAINT, PK_EIG_MAX, PK_EIG_CAND, PK_SELECT_FINISH, PK_COUNT };
+                PK_SET_MASK, PK_SHI_TOMASI, PK_SELECT_FINISH, PK_COUNT };
 
 struct Profiler {
     bool on = false;
@@ -63,6 +63,8 @@ struct vs_tracker {
     uint8_t* d_luts = nullptr;
     uint8_t* d_base_mask = nullptr;
     int* d_disc_hw = nullptr;
+    int* d_fish_hw = nullptr;     // row half widths of the auto fisheye circle
+    int base_mode = 0, fcx = 0, fcy = 0, fr = 0;   // StParams::base_mode and the circle
     double* d_cur_time = nullptr;
     float* d_eig = nullptr;       // lazily allocated dense eig map (stage API only)
     vs::GlueParams g{};

@@ -213,14 +213,275 @@ __global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_kernel(LkParams p) {
     }
 }
 
+// =================================================================================================
+// Fast path (win = 21): every lane owns two horizontal runs of 7 window pixels (21 rows x 3 runs = 63
+// runs for 32 lanes x 2).  Tiles are staged as aligned 32-bit words; a run reads 3 words per tile
+// row and re-aligns them with funnel shifts, the bilinear blend is two DP2A per pixel (16-bit
+// weights x u8 pixels), the Scharr derivatives five DP4A per sample, and the mismatch vector is
+// accumulated as sum(J*Ix) - sum(I*Ix) with the second term fixed per level.  All integer and
+// exact, so results are bit-identical to the generic kernel above.
+// =================================================================================================
+constexpr int kFastPitch = 36;                 // tile pitch in bytes (9 words)
+constexpr int kFastRows = 32;                  // search tile rows = win + 1 + 2 * margin
+constexpr int kFastWarpSmem = kFastPitch * kFastRows;
+
+__device__ __forceinline__ int dp2a_lo_su(int a, unsigned b, int c) {
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(int a, unsigned b, int c) {
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// stage nrows x nwords aligned words of a level into the warp's tile; x0 is a multiple of 4
+__device__ __forceinline__ void stage_words(uint32_t* tile, const uint8_t* __restrict__ img, int w, int h, int pitch,
+                                            int x0, int y0, int nrows, int nwords, int lane) {
+    for (int idx = lane; idx < nrows * nwords; idx += 32) {
+        const int r = idx / nwords, q = idx - r * nwords;
+        const int gx = x0 + 4 * q, gy = y0 + r;
+        uint32_t v;
+        if (gy >= 0 && gy < h && gx >= 0 && gx + 3 < w) {
+            v = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)gy * pitch + gx));
+        } else {
+            const uint8_t* row = img + (int64_t)reflect101(gy, h) * pitch;
+            v = (uint32_t)__ldg(row + reflect101(gx, w)) | ((uint32_t)__ldg(row + reflect101(gx + 1, w)) << 8) |
+                ((uint32_t)__ldg(row + reflect101(gx + 2, w)) << 16) | ((uint32_t)__ldg(row + reflect101(gx + 3, w)) << 24);
+        }
+        tile[r * (kFastPitch / 4) + q] = v;
+    }
+}
+
+// 12 bytes of a tile row starting at byte `sb`, re-aligned so that a0 holds bytes sb..sb+3, a1 sb+4..sb+7, a2 sb+8..sb+11
+__device__ __forceinline__ void load_aligned3(const uint32_t* trow, int sb, uint32_t& a0, uint32_t& a1, uint32_t& a2) {
+    const uint32_t* q = trow + (sb >> 2);
+    const int sh = (sb & 3) * 8;
+    const uint32_t w0 = q[0], w1 = q[1], w2 = q[2];
+    a0 = __funnelshift_r(w0, w1, sh);
+    a1 = __funnelshift_r(w1, w2, sh);
+    a2 = w2 >> sh;
+}
+
+__global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_fast21_kernel(LkParams p) {
+    constexpr int WIN = 21, NSEG = 3, NRUN = WIN * NSEG;
+    __shared__ __align__(16) uint32_t s_tiles[kLkWarpsPerCta][kFastWarpSmem / 4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int s = blockIdx.y;
+    const int i = blockIdx.x * kLkWarpsPerCta + warp;
+    const int n = p.counts[s];
+    if (i >= n) return;
+    uint32_t* tile = s_tiles[warp];
+    const float hw = (float)(WIN - 1) * 0.5f;
+
+    // this lane's two runs: run r -> window row r / 3, first window column 7 * (r % 3)
+    int rrow[2], rcol[2];
+    bool rok[2];
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+        const int r = lane + 32 * t;
+        rok[t] = r < NRUN;
+        const int rr = rok[t] ? r : 0;
+        rrow[t] = rr / NSEG;
+        rcol[t] = 7 * (rr - rrow[t] * NSEG);
+    }
+
+    const float2 pt = p.pts[(int64_t)s * p.cap + i];
+    float2 next = make_float2(0.f, 0.f);
+    int status = 1;
+    const uint8_t* prev_base = p.prev_pyr + (int64_t)s * p.pd.stream_bytes;
+    const uint8_t* next_base = p.next_pyr + (int64_t)s * p.pd.stream_bytes;
+    const int C3 = 0x000300FD, C10 = 0x000A00F6;        // Scharr x: (-3,0,3), (-10,0,10) as s8x4
+    const int CYP = 0x00030A03, CYN = 0x00FDF6FD;       // Scharr y: +(3,10,3) on row+1, -(3,10,3) on row-1
+
+    int ix[2][7], iy[2][7];      // interpolated template gradients
+    int c1[2], c2[2];            // sum(I * Ix), sum(I * Iy) of each run
+
+    for (int level = p.n_levels - 1; level >= 0; --level) {
+        const LevelDesc L = p.pd.lv[level];
+        const float lscale = 1.0f / (float)(1 << level);
+        const float2 prev_pt = make_float2(__fmul_rn(pt.x, lscale), __fmul_rn(pt.y, lscale));
+        if (level == p.n_levels - 1) next = prev_pt;
+        else next = make_float2(__fmul_rn(next.x, 2.0f), __fmul_rn(next.y, 2.0f));
+
+        const float ppx = __fsub_rn(prev_pt.x, hw), ppy = __fsub_rn(prev_pt.y, hw);
+        const int ipx = (int)floorf(ppx), ipy = (int)floorf(ppy);
+        if (ipx < -WIN || ipx >= L.w || ipy < -WIN || ipy >= L.h) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        int w00, w01, w10, w11;
+        lk_weights(__fsub_rn(ppx, (float)ipx), __fsub_rn(ppy, (float)ipy), w00, w01, w10, w11);
+        int wt = (w00 & 0xffff) | (w01 << 16), wb = (w10 & 0xffff) | (w11 << 16);
+
+        // ---- template: tile origin (x aligned down to 4, ipy - 1), 24 rows x 8 words ----
+        const int tx0 = (ipx - 1) & ~3, ax = (ipx - 1) - tx0;
+        __syncwarp();
+        stage_words(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, WIN + 3, 8, lane);
+        __syncwarp();
+        const bool border = ipx < 0 || ipy < 0 || ipx + WIN + 1 > L.w || ipy + WIN + 1 > L.h;
+        int s11 = 0, s12 = 0, s22 = 0;
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            c1[t] = 0;
+            c2[t] = 0;
+            // derivative samples j = 0..7 of window rows rrow, rrow+1 need tile rows rrow .. rrow+3 and
+            // bytes sb .. sb+9 with sb = ax + rcol (one left of the first sample)
+            const int sb = ax + rcol[t];
+            uint32_t S[4][8];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                // 10 bytes sb .. sb+9 can straddle four aligned words
+                const uint32_t* q = tile + (rrow[t] + r) * (kFastPitch / 4) + (sb >> 2);
+                const int sh = (sb & 3) * 8;
+                const uint32_t a0 = __funnelshift_r(q[0], q[1], sh), a1 = __funnelshift_r(q[1], q[2], sh),
+                               a2 = __funnelshift_r(q[2], q[3], sh);
+                S[r][0] = a0;
+                S[r][1] = __funnelshift_r(a0, a1, 8);
+                S[r][2] = __funnelshift_r(a0, a1, 16);
+                S[r][3] = __funnelshift_r(a0, a1, 24);
+                S[r][4] = a1;
+                S[r][5] = __funnelshift_r(a1, a2, 8);
+                S[r][6] = __funnelshift_r(a1, a2, 16);
+                S[r][7] = __funnelshift_r(a1, a2, 24);
+            }
+            int dx0[8], dy0[8], dx1[8], dy1[8];   // derivative rows rrow and rrow + 1
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                dx0[j] = dp4a_us(S[2][j], C3, dp4a_us(S[1][j], C10, dp4a_us(S[0][j], C3, 0)));
+                dx1[j] = dp4a_us(S[3][j], C3, dp4a_us(S[2][j], C10, dp4a_us(S[1][j], C3, 0)));
+                dy0[j] = dp4a_us(S[2][j], CYP, dp4a_us(S[0][j], CYN, 0));
+                dy1[j] = dp4a_us(S[3][j], CYP, dp4a_us(S[1][j], CYN, 0));
+            }
+            if (border) {   // derivative image is zero-padded (BORDER_CONSTANT) outside the level
+                const int gy0 = ipy + rrow[t], gx0 = ipx + rcol[t];
+                const bool y0ok = gy0 >= 0 && gy0 < L.h, y1ok = gy0 + 1 >= 0 && gy0 + 1 < L.h;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const bool xok = gx0 + j >= 0 && gx0 + j < L.w;
+                    if (!(xok && y0ok)) { dx0[j] = 0; dy0[j] = 0; }
+                    if (!(xok && y1ok)) { dx1[j] = 0; dy1[j] = 0; }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 7; ++j) {
+                const int gx = (dx0[j] * w00 + dx0[j + 1] * w01 + dx1[j] * w10 + dx1[j + 1] * w11 + 8192) >> 14;
+                const int gy = (dy0[j] * w00 + dy0[j + 1] * w01 + dy1[j] * w10 + dy1[j + 1] * w11 + 8192) >> 14;
+                // template intensity: bytes (x, x+1) of tile rows rrow+1, rrow+2 = low half of S[.][j+1]
+                const int iv = dp2a_lo_su(wb, S[2][j + 1], dp2a_lo_su(wt, S[1][j + 1], 256)) >> 9;
+                const bool ok = rok[t];
+                ix[t][j] = ok ? gx : 0;
+                iy[t][j] = ok ? gy : 0;
+                s11 += ix[t][j] * ix[t][j];
+                s12 += ix[t][j] * iy[t][j];
+                s22 += iy[t][j] * iy[t][j];
+                c1[t] += iv * ix[t][j];
+                c2[t] += iv * iy[t][j];
+            }
+        }
+        const float kScale = 1.0f / (float)(1 << 20);
+        const float A11 = __fmul_rn(__ll2float_rn(warp_sum_exact(s11)), kScale);
+        const float A12 = __fmul_rn(__ll2float_rn(warp_sum_exact(s12)), kScale);
+        const float A22 = __fmul_rn(__ll2float_rn(warp_sum_exact(s22)), kScale);
+        float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
+        const float dA = __fsub_rn(A11, A22);
+        const float disc = __fadd_rn(__fmul_rn(dA, dA), __fmul_rn(__fmul_rn(4.0f, A12), A12));
+        const float min_eig = __fdiv_rn(__fsub_rn(__fadd_rn(A22, A11), __fsqrt_rn(disc)), (float)(2 * WIN * WIN));
+        if (min_eig < p.min_eig_threshold || D < 1.1920928955078125e-07f) {
+            if (level == 0) status = 0;
+            continue;
+        }
+        D = __fdiv_rn(1.0f, D);
+
+        // ---- iterations on the next image ----
+        float qx = __fsub_rn(next.x, hw), qy = __fsub_rn(next.y, hw);
+        float pdx = 0.f, pdy = 0.f;
+        const uint8_t* J = next_base + L.offset;
+        int tox = 0, toy = 0;          // image coordinates of tile byte (0, 0); tox is a multiple of 4
+        bool staged = false;
+        for (int j = 0; j < p.max_count; ++j) {
+            const int iqx = (int)floorf(qx), iqy = (int)floorf(qy);
+            if (iqx < -WIN || iqx >= L.w || iqy < -WIN || iqy >= L.h) {
+                if (level == 0) status = 0;
+                break;
+            }
+            // the tile must hold columns iqx .. iqx+21 (+ alignment slack) and rows iqy .. iqy+21
+            if (!staged || iqx < tox || iqx + WIN + 1 + 3 > tox + kFastPitch || iqy < toy || iqy + WIN + 1 > toy + kFastRows) {
+                tox = (iqx - kLkMargin) & ~3;
+                toy = iqy - kLkMargin;
+                __syncwarp();
+                stage_words(tile, J, L.w, L.h, L.pitch, tox, toy, kFastRows, kFastPitch / 4, lane);
+                __syncwarp();
+                staged = true;
+            }
+            lk_weights(__fsub_rn(qx, (float)iqx), __fsub_rn(qy, (float)iqy), w00, w01, w10, w11);
+            wt = (w00 & 0xffff) | (w01 << 16);
+            wb = (w10 & 0xffff) | (w11 << 16);
+            int sb1 = 0, sb2 = 0;
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int sb = iqx - tox + rcol[t];
+                const uint32_t* trow = tile + (iqy - toy + rrow[t]) * (kFastPitch / 4);
+                uint32_t a0, a1, a2, b0, b1, b2;
+                load_aligned3(trow, sb, a0, a1, a2);
+                load_aligned3(trow + kFastPitch / 4, sb, b0, b1, b2);
+                const uint32_t a01 = __funnelshift_r(a0, a1, 8), a12 = a1 >> 8;
+                const uint32_t b01 = __funnelshift_r(b0, b1, 8), b12 = b1 >> 8;
+                int jv[7];
+                jv[0] = dp2a_lo_su(wb, b0, dp2a_lo_su(wt, a0, 256));
+                jv[1] = dp2a_lo_su(wb, b01, dp2a_lo_su(wt, a01, 256));
+                jv[2] = dp2a_hi_su(wb, b0, dp2a_hi_su(wt, a0, 256));
+                jv[3] = dp2a_hi_su(wb, b01, dp2a_hi_su(wt, a01, 256));
+                jv[4] = dp2a_lo_su(wb, b1, dp2a_lo_su(wt, a1, 256));
+                jv[5] = dp2a_lo_su(wb, b12, dp2a_lo_su(wt, a12, 256));
+                jv[6] = dp2a_hi_su(wb, b1, dp2a_hi_su(wt, a1, 256));
+                int t1 = -c1[t], t2 = -c2[t];
+#pragma unroll
+                for (int k = 0; k < 7; ++k) {
+                    const int v = jv[k] >> 9;
+                    t1 += v * ix[t][k];
+                    t2 += v * iy[t][k];
+                }
+                sb1 += t1;
+                sb2 += t2;
+            }
+            const float b1 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb1)), kScale);
+            const float b2 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb2)), kScale);
+            const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
+            const float dy = __fmul_rn(__fsub_rn(__fmul_rn(A12, b1), __fmul_rn(A11, b2)), D);
+            qx = __fadd_rn(qx, dx);
+            qy = __fadd_rn(qy, dy);
+            next = make_float2(__fadd_rn(qx, hw), __fadd_rn(qy, hw));
+            if ((double)dx * (double)dx + (double)dy * (double)dy <= p.eps2) break;
+            if (j > 0 && fabs((double)__fadd_rn(dx, pdx)) < 0.01 && fabs((double)__fadd_rn(dy, pdy)) < 0.01) {
+                next.x = __fsub_rn(next.x, __fmul_rn(dx, 0.5f));
+                next.y = __fsub_rn(next.y, __fmul_rn(dy, 0.5f));
+                break;
+            }
+            pdx = dx;
+            pdy = dy;
+        }
+    }
+    if (lane == 0) {
+        p.next_pts[(int64_t)s * p.cap + i] = next;
+        p.status[(int64_t)s * p.cap + i] = (uint8_t)status;
+    }
+}
+
 int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches) {
     if (p.win < 3 || p.win > kMaxWin || (p.win & 1) == 0) return -1;
     if (max_features <= 0 || p.n_levels <= 0) return 0;
-    const int smem = kLkWarpsPerCta * lk_warp_smem(p.win);
     dim3 grid((max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta, n_streams);
     if (p.win == 21) {
-        lk_kernel<21><<<grid, 32 * kLkWarpsPerCta, smem, st>>>(p);
+        lk_fast21_kernel<<<grid, 32 * kLkWarpsPerCta, 0, st>>>(p);
     } else {
+        const int smem = kLkWarpsPerCta * lk_warp_smem(p.win);
         static bool attr_set = false;
         if (!attr_set) {
             cudaFuncSetAttribute(lk_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,

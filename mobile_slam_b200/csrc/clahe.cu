@@ -2,17 +2,165 @@
 // Replaces the clahe_->apply call at /root/reference/src/frontend/feature_tracker.cpp:102-106.
 // Arithmetic spec: SURVEY.md S1 (integer histogram/clip/redistribute, float32 LUT scale and
 // bilinear LUT blend with no FMA contraction, round-half-even).
+#include <cuda_fp16.h>
+
+#include <cmath>
+
 #include "kernels.h"
 
 namespace vs {
 
 // ---------------------------------------------------------------------------------------------
 // K1: one CTA per (tile, stream): 256-bin histogram -> clip -> redistribute -> scan -> LUT.
+//
+// Histogram without atomics: every thread owns a private set of 256 byte counters, packed four to a
+// 32-bit word (bins v, v+64, v+128, v+192 share word row v & 63) and laid out so that thread t only
+// ever touches shared-memory bank t % 32 — the read-modify-write of a pixel is conflict free no
+// matter which bins the 32 lanes of a warp hit.  A thread sees at most 255 pixels (the launcher
+// picks the CTA size from the tile area), so the byte counters cannot overflow.  The private
+// counters are then summed with packed 16-bit adds.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) clahe_lut_kernel(const uint8_t* __restrict__ src, int pitch,
-                                                        int64_t img_stride, int W, int H, int tw, int th,
-                                                        int clip, float lut_scale,
-                                                        uint8_t* __restrict__ luts) {
+template <int NT>
+__global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict__ src, int pitch, int64_t img_stride,
+                                                       int tw, int th, int clip, float lut_scale,
+                                                       uint8_t* __restrict__ luts) {
+    extern __shared__ __align__(16) uint32_t s_cnt[];          // [64 word rows][NT threads]
+    __shared__ uint32_t s_part[NT / 64][64][2];
+    __shared__ int s_hist[256];
+    __shared__ unsigned int s_warp_tot[NT / 32];
+    __shared__ unsigned int s_clipped;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x, s = blockIdx.y;
+    const int tx = tile % kClaheTiles, ty = tile / kClaheTiles;
+    const uint8_t* img = src + (int64_t)s * img_stride;
+#pragma unroll 4
+    for (int r = 0; r < 64; ++r) s_cnt[r * NT + tid] = 0;
+    if (tid == 0) s_clipped = 0;
+    // no barrier needed before the pixel loop: a thread only touches its own column of s_cnt
+
+    // aligned words covering the tile's columns [x0, x0 + tw); the first / last word may be partial
+    const int x0 = tx * tw, y0 = ty * th;
+    const int xa = x0 & ~3, nw = ((x0 + tw - 1) >> 2) - (xa >> 2) + 1;
+    uint32_t* mine = s_cnt + tid;
+    const int total = nw * th;
+    for (int idx0 = tid; idx0 < total; idx0 += 4 * NT) {
+        // four independent loads in flight per thread before the dependent shared-memory updates
+        uint32_t v[4];
+        int k0[4], k1[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int idx = idx0 + u * NT;
+            const int ic = min(idx, total - 1);
+            const int y = ic / nw, q = ic - y * nw;
+            const int xw = xa + 4 * q;
+            v[u] = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)(y0 + y) * pitch + xw));
+            k0[u] = max(x0 - xw, 0);
+            k1[u] = idx < total ? min(x0 + tw - xw, 4) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            uint32_t w = v[u] >> (8 * k0[u]);
+            for (int k = k0[u]; k < k1[u]; ++k) {
+                const uint32_t b = w & 255u;
+                w >>= 8;
+                mine[(b & 63u) * NT] += 1u << ((b >> 6) * 8);
+            }
+        }
+    }
+    __syncthreads();
+    // sum the NT private copies: thread -> (word row r, 64-column group cg), rotated so lanes hit distinct banks
+    {
+        const int r = tid & 63, cg = tid >> 6;
+        uint32_t a = 0, b = 0;      // packed 16-bit sums of bytes (0, 2) and (1, 3)
+        const uint32_t* row = s_cnt + r * NT + cg * 64;
+#pragma unroll 8
+        for (int j = 0; j < 64; ++j) {
+            const uint32_t w = row[(j + lane) & 63];
+            a += w & 0x00FF00FFu;
+            b += (w >> 8) & 0x00FF00FFu;
+        }
+        s_part[cg][r][0] = a;
+        s_part[cg][r][1] = b;
+    }
+    __syncthreads();
+    if (tid < 64) {
+        uint32_t a = 0, b = 0;
+#pragma unroll
+        for (int cg = 0; cg < NT / 64; ++cg) {     // per-16-bit-lane totals stay below 65536 (tile area checked by the launcher)
+            a += s_part[cg][tid][0];
+            b += s_part[cg][tid][1];
+        }
+        s_hist[tid] = (int)(a & 0xFFFFu);            // byte 0 -> bin r
+        s_hist[tid + 64] = (int)(b & 0xFFFFu);       // byte 1 -> bin r + 64
+        s_hist[tid + 128] = (int)(a >> 16);          // byte 2 -> bin r + 128
+        s_hist[tid + 192] = (int)(b >> 16);          // byte 3 -> bin r + 192
+    }
+    __syncthreads();
+    // clip, count the excess; thread t owns bins t*BPT .. t*BPT+BPT-1
+    constexpr int BPT = 256 / NT;
+    int h[BPT];
+    unsigned int e = 0;
+#pragma unroll
+    for (int k = 0; k < BPT; ++k) {
+        h[k] = s_hist[tid * BPT + k];
+        if (h[k] > clip) {
+            e += (unsigned int)(h[k] - clip);
+            h[k] = clip;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
+    if (lane == 0 && e) atomicAdd(&s_clipped, e);
+    __syncthreads();
+    const int clipped = (int)s_clipped;
+    const int residual = clipped & 255;    // clipped % 256
+    int step = residual ? 256 / residual : 1;
+    if (step < 1) step = 1;
+    unsigned int run = 0;
+#pragma unroll
+    for (int k = 0; k < BPT; ++k) {
+        const int bin = tid * BPT + k;
+        h[k] += clipped >> 8;              // clipped / 256
+        // serial loop "for (i = 0; i < 256 && residual > 0; i += step, residual--) hist[i]++"
+        if (residual && (bin % step) == 0 && (bin / step) < residual) h[k] += 1;
+        run += (unsigned int)h[k];
+        h[k] = (int)run;                   // inclusive prefix inside the thread
+    }
+    unsigned int v = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+    }
+    if (lane == 31) s_warp_tot[warp] = v;
+    __syncthreads();
+    unsigned int base = v - run;
+#pragma unroll
+    for (int k = 0; k < NT / 32; ++k)
+        if (k < warp) base += s_warp_tot[k];
+    uint32_t packed = 0;
+#pragma unroll
+    for (int k = 0; k < BPT; ++k) {
+        int q = __float2int_rn(__fmul_rn((float)(int)(base + (unsigned int)h[k]), lut_scale));
+        q = q < 0 ? 0 : (q > 255 ? 255 : q);
+        packed |= (uint32_t)q << (8 * (k & 3));
+        if ((k & 3) == 3 || k == BPT - 1) {
+            uint8_t* d = luts + ((int64_t)s * (kClaheTiles * kClaheTiles) + tile) * 256 + tid * BPT + (k & ~3);
+            if (BPT >= 4) *reinterpret_cast<uint32_t*>(d) = packed;
+            else
+                for (int j = 0; j <= (k & 3); ++j) d[j] = (uint8_t)(packed >> (8 * j));
+            packed = 0;
+        }
+    }
+}
+
+// Generic K1 (images whose size is not a multiple of 8, or tiles above 65 280 pixels): shared-memory
+// atomics on warp-private sub-histograms, pixels fetched one by one with the REFLECT_101 padding
+// cv::CLAHE applies to the bottom/right.
+__global__ void __launch_bounds__(256) clahe_lut_generic_kernel(const uint8_t* __restrict__ src, int pitch,
+                                                                int64_t img_stride, int W, int H, int tw, int th,
+                                                                int clip, float lut_scale,
+                                                                uint8_t* __restrict__ luts) {
     __shared__ unsigned int hist[8][256];
     __shared__ unsigned int warp_tot[8];
     __shared__ unsigned int s_clipped;
@@ -24,34 +172,16 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const uint8_t* __restric
     for (int k = 0; k < 8; ++k) hist[k][tid] = 0;
     if (tid == 0) s_clipped = 0;
     __syncthreads();
-
     const int x0 = tx * tw, y0 = ty * th;
-    const bool interior = (x0 + tw <= W) && (y0 + th <= H);
-    if (interior && ((tw & 3) == 0) && ((pitch & 3) == 0)) {
-        // fast path: 4 pixels per 32-bit load, tile rows are 4-byte aligned (x0 = tx*tw)
-        const int wq = tw >> 2;
-        for (int idx = tid; idx < wq * th; idx += 256) {
-            const int y = idx / wq, xq = idx - y * wq;
-            const uint32_t v = *reinterpret_cast<const uint32_t*>(img + (int64_t)(y0 + y) * pitch + x0 + 4 * xq);
-            atomicAdd(&hist[warp][v & 255u], 1u);
-            atomicAdd(&hist[warp][(v >> 8) & 255u], 1u);
-            atomicAdd(&hist[warp][(v >> 16) & 255u], 1u);
-            atomicAdd(&hist[warp][v >> 24], 1u);
-        }
-    } else {
-        // general path: the image is virtually padded bottom/right with REFLECT_101 to 8x8 tiles
-        for (int idx = tid; idx < tw * th; idx += 256) {
-            const int y = idx / tw, x = idx - y * tw;
-            const int gx = reflect101(x0 + x, W), gy = reflect101(y0 + y, H);
-            atomicAdd(&hist[warp][img[(int64_t)gy * pitch + gx]], 1u);
-        }
+    for (int idx = tid; idx < tw * th; idx += 256) {
+        const int y = idx / tw, x = idx - y * tw;
+        const int gx = reflect101(x0 + x, W), gy = reflect101(y0 + y, H);
+        atomicAdd(&hist[warp][img[(int64_t)gy * pitch + gx]], 1u);
     }
     __syncthreads();
     int h = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) h += (int)hist[k][tid];
-
-    // clip and count the excess
     int excess = h > clip ? h - clip : 0;
     h = h > clip ? clip : h;
     unsigned int e = (unsigned int)excess;
@@ -60,15 +190,13 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const uint8_t* __restric
     if (lane == 0 && e) atomicAdd(&s_clipped, e);
     __syncthreads();
     const int clipped = (int)s_clipped;
-    h += clipped >> 8;                     // clipped / 256
-    const int residual = clipped & 255;    // clipped % 256
+    h += clipped >> 8;
+    const int residual = clipped & 255;
     if (residual) {
         int step = 256 / residual;
         if (step < 1) step = 1;
-        // serial loop "for (i = 0; i < 256 && residual > 0; i += step, residual--) hist[i]++"
         if ((tid % step) == 0 && (tid / step) < residual) h += 1;
     }
-    // inclusive scan over the 256 bins
     unsigned int v = (unsigned int)h;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -81,86 +209,114 @@ __global__ void __launch_bounds__(256) clahe_lut_kernel(const uint8_t* __restric
 #pragma unroll
     for (int k = 0; k < 8; ++k)
         if (k < warp) base += warp_tot[k];
-    const float sum = (float)(int)(v + base);
-    int q = __float2int_rn(__fmul_rn(sum, lut_scale));
+    int q = __float2int_rn(__fmul_rn((float)(int)(v + base), lut_scale));
     q = q < 0 ? 0 : (q > 255 ? 255 : q);
     luts[((int64_t)s * (kClaheTiles * kClaheTiles) + tile) * 256 + tid] = (uint8_t)q;
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2: bilinear blend of the four neighbouring tile LUTs.  One CTA = a band of kBandRows rows.
+// K2: bilinear blend of the four neighbouring tile LUTs.
+//
+// One CTA = one interpolation band (the rows that share the same pair of tile rows) x one chunk of
+// 128 columns.  The CTA first gathers, for every interpolation cell its chunk touches, a table of
+// 256 entries holding the four LUT values a pixel of that cell needs (as 4 x fp16, exact for 0..255),
+// so a pixel costs ONE 8-byte shared-memory load instead of four byte loads; then each warp walks
+// down the band, one aligned 32-bit word (4 pixels) per lane and row, with the per-column weights
+// held in registers.
 // ---------------------------------------------------------------------------------------------
-constexpr int kBandRows = 16;
+constexpr int kApplyThreads = 256;
+constexpr int kApplyMaxCells = 9;
 
-__device__ __forceinline__ uint32_t clahe_px(const uint8_t* __restrict__ lut_lo,
-                                             const uint8_t* __restrict__ lut_hi, int tx1, int tx2,
-                                             float xa, float xa1, float ya, float ya1, uint32_t v) {
-    const float p1 = (float)lut_lo[tx1 * 256 + v];
-    const float p2 = (float)lut_lo[tx2 * 256 + v];
-    const float q1 = (float)lut_hi[tx1 * 256 + v];
-    const float q2 = (float)lut_hi[tx2 * 256 + v];
-    const float top = __fadd_rn(__fmul_rn(p1, xa1), __fmul_rn(p2, xa));
-    const float bot = __fadd_rn(__fmul_rn(q1, xa1), __fmul_rn(q2, xa));
-    const float r = __fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya));
-    int q = __float2int_rn(r);
-    q = q < 0 ? 0 : (q > 255 ? 255 : q);
-    return (uint32_t)q;
+struct ClaheBands {
+    int start[kClaheTiles + 2];   // band b (cell row b-1) covers rows start[b] .. start[b+1]-1
+};
+
+__device__ __forceinline__ float round_magic(float r) {   // round-half-even of 0 <= r <= 255 into the low byte
+    return __fadd_rn(r, 12582912.0f);
 }
 
-__global__ void __launch_bounds__(256) clahe_apply_kernel(const uint8_t* __restrict__ src, int src_pitch,
-                                                          int64_t src_stride, uint8_t* __restrict__ dst,
-                                                          int dst_pitch, int64_t dst_stride, int W, int H,
-                                                          float inv_tw, float inv_th,
-                                                          const uint8_t* __restrict__ luts) {
-    __shared__ __align__(16) uint8_t s_lut[kClaheTiles * kClaheTiles * 256];
-    const int tid = threadIdx.x;
+__global__ void __launch_bounds__(kApplyThreads) clahe_apply_kernel(const uint8_t* __restrict__ src, int src_pitch,
+                                                                    int64_t src_stride, uint8_t* __restrict__ dst,
+                                                                    int dst_pitch, int64_t dst_stride, int W, int H,
+                                                                    float inv_tw, float inv_th, ClaheBands bands,
+                                                                    int nchunks, const uint8_t* __restrict__ luts) {
+    __shared__ __align__(16) uint2 s_cell[kApplyMaxCells][256];     // (p1, p2, q1, q2) as 4 x fp16
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int s = blockIdx.y;
-    const int y_begin = blockIdx.x * kBandRows;
-    const int y_end = min(y_begin + kBandRows, H);
-    // tile rows touched by this band
-    const int ty_first = max((int)floorf(__fsub_rn(__fmul_rn((float)y_begin, inv_th), 0.5f)), 0);
-    const int ty_last = min((int)floorf(__fsub_rn(__fmul_rn((float)(y_end - 1), inv_th), 0.5f)) + 1, kClaheTiles - 1);
-    {
-        const uint4* g = reinterpret_cast<const uint4*>(luts + (int64_t)s * (kClaheTiles * kClaheTiles * 256));
-        uint4* d = reinterpret_cast<uint4*>(s_lut);
-        const int lo = ty_first * (kClaheTiles * 256 / 16), hi = (ty_last + 1) * (kClaheTiles * 256 / 16);
-        for (int i = lo + tid; i < hi; i += 256) d[i] = g[i];
+    const int band = blockIdx.x / nchunks, chunk = blockIdx.x - band * nchunks;
+    const int y_begin = bands.start[band], y_end = bands.start[band + 1];
+    if (y_begin >= y_end) return;
+    const int cy = band - 1;                                         // cell row: tile rows (cy, cy+1) clamped
+    const int ty1 = max(cy, 0), ty2 = min(cy + 1, kClaheTiles - 1);
+    const int xc0 = chunk * 128, xc1 = min(xc0 + 128, W) - 1;
+    const int cell_first = (int)floorf(__fsub_rn(__fmul_rn((float)xc0, inv_tw), 0.5f));
+    const int cell_last = (int)floorf(__fsub_rn(__fmul_rn((float)xc1, inv_tw), 0.5f));
+    const int ncell = cell_last - cell_first + 1;
+    const uint8_t* L = luts + (int64_t)s * (kClaheTiles * kClaheTiles * 256);
+    for (int idx = tid; idx < ncell * 256; idx += kApplyThreads) {
+        const int c = idx >> 8, v = idx & 255;
+        const int cx = cell_first + c;
+        const int tx1 = max(cx, 0), tx2 = min(cx + 1, kClaheTiles - 1);
+        const __half2 top = __halves2half2(__ushort2half_rn(L[(ty1 * kClaheTiles + tx1) * 256 + v]),
+                                           __ushort2half_rn(L[(ty1 * kClaheTiles + tx2) * 256 + v]));
+        const __half2 bot = __halves2half2(__ushort2half_rn(L[(ty2 * kClaheTiles + tx1) * 256 + v]),
+                                           __ushort2half_rn(L[(ty2 * kClaheTiles + tx2) * 256 + v]));
+        s_cell[c][v] = make_uint2(*reinterpret_cast<const uint32_t*>(&top), *reinterpret_cast<const uint32_t*>(&bot));
+    }
+    // per-lane column constants: word x = xc0 + 4*lane
+    const int x = xc0 + 4 * lane;
+    float xa[4], xa1[4];
+    const uint2* cellp[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float txf = __fsub_rn(__fmul_rn((float)(x + k), inv_tw), 0.5f);
+        const int tx1r = (int)floorf(txf);
+        xa[k] = __fsub_rn(txf, (float)tx1r);
+        xa1[k] = __fsub_rn(1.0f, xa[k]);
+        cellp[k] = s_cell[min(max(tx1r - cell_first, 0), kApplyMaxCells - 1)];
     }
     __syncthreads();
-    const uint8_t* img = src + (int64_t)s * src_stride;
-    uint8_t* out = dst + (int64_t)s * dst_stride;
-    const int wq = (W + 3) >> 2;
-    const int rows = y_end - y_begin;
-    for (int idx = tid; idx < wq * rows; idx += 256) {
-        const int r = idx / wq, xq = idx - r * wq;
-        const int y = y_begin + r, x = xq << 2;
+    if (x >= W) return;
+    const uint8_t* img = src + (int64_t)s * src_stride + x;
+    uint8_t* out = dst + (int64_t)s * dst_stride + x;
+    const bool full = (x + 3 < W);
+    auto fetch = [&](int y) -> uint32_t {
+        if (y >= y_end) return 0u;
+        const uint8_t* sp = img + (int64_t)y * src_pitch;
+        if (full) return __ldg(reinterpret_cast<const uint32_t*>(sp));
+        uint32_t v4 = 0;
+        for (int k = 0; k < 4 && x + k < W; ++k) v4 |= (uint32_t)sp[k] << (8 * k);
+        return v4;
+    };
+    auto process = [&](int y, uint32_t v4) {
+        if (y >= y_end) return;
         const float tyf = __fsub_rn(__fmul_rn((float)y, inv_th), 0.5f);
-        const int ty1r = (int)floorf(tyf);
-        const float ya = __fsub_rn(tyf, (float)ty1r), ya1 = __fsub_rn(1.0f, ya);
-        const int ty1 = max(ty1r, 0), ty2 = min(ty1r + 1, kClaheTiles - 1);
-        const uint8_t* lut_lo = s_lut + ty1 * (kClaheTiles * 256);
-        const uint8_t* lut_hi = s_lut + ty2 * (kClaheTiles * 256);
-        const uint8_t* sp = img + (int64_t)y * src_pitch + x;
-        uint8_t* dp = out + (int64_t)y * dst_pitch + x;
-        uint32_t v4;
-        const bool full = (x + 3 < W);
-        if (full) v4 = *reinterpret_cast<const uint32_t*>(sp);
-        else {
-            v4 = 0;
-            for (int k = 0; k < 4 && x + k < W; ++k) v4 |= (uint32_t)sp[k] << (8 * k);
-        }
+        const float ya = __fsub_rn(tyf, floorf(tyf)), ya1 = __fsub_rn(1.0f, ya);
         uint32_t o4 = 0;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const float txf = __fsub_rn(__fmul_rn((float)(x + k), inv_tw), 0.5f);
-            const int tx1r = (int)floorf(txf);
-            const float xa = __fsub_rn(txf, (float)tx1r), xa1 = __fsub_rn(1.0f, xa);
-            const int tx1 = max(tx1r, 0), tx2 = min(tx1r + 1, kClaheTiles - 1);
-            o4 |= clahe_px(lut_lo, lut_hi, tx1, tx2, xa, xa1, ya, ya1, (v4 >> (8 * k)) & 255u) << (8 * k);
+            const uint2 ent = cellp[k][(v4 >> (8 * k)) & 255u];
+            const float2 pt = __half22float2(*reinterpret_cast<const __half2*>(&ent.x));
+            const float2 pb = __half22float2(*reinterpret_cast<const __half2*>(&ent.y));
+            const float top = __fadd_rn(__fmul_rn(pt.x, xa1[k]), __fmul_rn(pt.y, xa[k]));
+            const float bot = __fadd_rn(__fmul_rn(pb.x, xa1[k]), __fmul_rn(pb.y, xa[k]));
+            const float r = __fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya));
+            // 0 <= r <= 255 (convex blend of bytes), so saturate_cast is the identity after rounding
+            o4 |= (__float_as_uint(round_magic(r)) & 255u) << (8 * k);
         }
+        uint8_t* dp = out + (int64_t)y * dst_pitch;
         if (full) *reinterpret_cast<uint32_t*>(dp) = o4;
         else
             for (int k = 0; k < 4 && x + k < W; ++k) dp[k] = (uint8_t)(o4 >> (8 * k));
+    };
+    constexpr int RS = kApplyThreads / 32;       // row stride between a warp's rows
+    for (int y = y_begin + warp; y < y_end; y += 4 * RS) {
+        // four rows in flight per lane before the dependent LUT lookups
+        const uint32_t a0 = fetch(y), a1 = fetch(y + RS), a2 = fetch(y + 2 * RS), a3 = fetch(y + 3 * RS);
+        process(y, a0);
+        process(y + RS, a1);
+        process(y + 2 * RS, a2);
+        process(y + 3 * RS, a3);
     }
 }
 
@@ -181,42 +337,78 @@ __global__ void __launch_bounds__(256) copy_image_kernel(const uint8_t* __restri
     }
 }
 
-void launch_clahe(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,
-                  int64_t dst_stride, int W, int H, int n_streams, uint8_t* luts, cudaStream_t st,
-                  int64_t* launches) {
+struct ClaheGeom {
+    int tw, th, clip;
+    float lut_scale;
+};
+static ClaheGeom clahe_geom(int W, int H) {
     const int We = (W + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
     const int He = (H + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
-    const int tw = We / kClaheTiles, th = He / kClaheTiles;
-    const int area = tw * th;
-    int clip = (int)(3.0 * area / 256);   // clipLimit * tileSizeTotal / histSize
-    if (clip < 1) clip = 1;
-    const float lut_scale = 255.0f / (float)area;
-    clahe_lut_kernel<<<dim3(kClaheTiles * kClaheTiles, n_streams), 256, 0, st>>>(
-        src, src_pitch, src_stride, W, H, tw, th, clip, lut_scale, luts);
-    clahe_apply_kernel<<<dim3((H + kBandRows - 1) / kBandRows, n_streams), 256, 0, st>>>(
-        src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, 1.0f / (float)tw, 1.0f / (float)th, luts);
-    if (launches) *launches += 2;
+    ClaheGeom g;
+    g.tw = We / kClaheTiles;
+    g.th = He / kClaheTiles;
+    const int area = g.tw * g.th;
+    g.clip = (int)(3.0 * area / 256);   // clipLimit * tileSizeTotal / histSize
+    if (g.clip < 1) g.clip = 1;
+    g.lut_scale = 255.0f / (float)area;
+    return g;
+}
+
+template <int NT>
+static void launch_lut_nt(const uint8_t* src, int src_pitch, int64_t src_stride, const ClaheGeom& g, int n_streams,
+                          uint8_t* luts, cudaStream_t st) {
+    const int smem = 64 * NT * 4;
+    static bool configured = false;
+    if (!configured && smem > 48 * 1024) {
+        cudaFuncSetAttribute(clahe_lut_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured = true;
+    }
+    clahe_lut_kernel<NT><<<dim3(kClaheTiles * kClaheTiles, n_streams), NT, smem, st>>>(
+        src, src_pitch, src_stride, g.tw, g.th, g.clip, g.lut_scale, luts);
 }
 
 void launch_clahe_lut_only(const uint8_t* src, int src_pitch, int64_t src_stride, int W, int H, int n_streams,
                            uint8_t* luts, cudaStream_t st) {
-    const int We = (W + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
-    const int He = (H + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
-    const int tw = We / kClaheTiles, th = He / kClaheTiles;
-    int clip = (int)(3.0 * (tw * th) / 256);
-    if (clip < 1) clip = 1;
-    clahe_lut_kernel<<<dim3(kClaheTiles * kClaheTiles, n_streams), 256, 0, st>>>(
-        src, src_pitch, src_stride, W, H, tw, th, clip, 255.0f / (float)(tw * th), luts);
+    const ClaheGeom g = clahe_geom(W, H);
+    const int area = g.tw * g.th;
+    const bool exact_tiles = (W % kClaheTiles == 0) && (H % kClaheTiles == 0) && (src_pitch % 4 == 0);
+    // a thread of the private-counter kernel may see up to 4 * ceil(words/NT) pixels; keep that below 256
+    const int words = ((g.tw + 6) / 4 + 1) * g.th;
+    if (exact_tiles && 4 * ((words + 63) / 64) <= 255) launch_lut_nt<64>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    else if (exact_tiles && 4 * ((words + 127) / 128) <= 255) launch_lut_nt<128>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    else if (exact_tiles && 4 * ((words + 255) / 256) <= 255 && area < 65536) launch_lut_nt<256>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    else
+        clahe_lut_generic_kernel<<<dim3(kClaheTiles * kClaheTiles, n_streams), 256, 0, st>>>(
+            src, src_pitch, src_stride, W, H, g.tw, g.th, g.clip, g.lut_scale, luts);
 }
 
 void launch_clahe_apply_only(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,
                              int64_t dst_stride, int W, int H, int n_streams, const uint8_t* luts,
                              cudaStream_t st) {
-    const int We = (W + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
-    const int He = (H + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
-    const int tw = We / kClaheTiles, th = He / kClaheTiles;
-    clahe_apply_kernel<<<dim3((H + kBandRows - 1) / kBandRows, n_streams), 256, 0, st>>>(
-        src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, 1.0f / (float)tw, 1.0f / (float)th, luts);
+    const ClaheGeom g = clahe_geom(W, H);
+    const float inv_tw = 1.0f / (float)g.tw, inv_th = 1.0f / (float)g.th;
+    // interpolation bands: rows grouped by floor(y * inv_th - 0.5f), evaluated in float32 exactly like the kernel
+    ClaheBands bands;
+    int b = 0;
+    bands.start[0] = 0;
+    for (int y = 0; y < H; ++y) {
+        volatile float prod = (float)y * inv_th;     // two separately rounded float32 operations, like the kernel
+        volatile float tyf = prod - 0.5f;
+        const int cy = (int)std::floor(tyf);
+        while (b < cy + 1 && b < kClaheTiles) bands.start[++b] = y;
+    }
+    while (b < kClaheTiles + 1) bands.start[++b] = H;
+    const int nchunks = (W + 127) / 128;
+    clahe_apply_kernel<<<dim3((kClaheTiles + 1) * nchunks, n_streams), kApplyThreads, 0, st>>>(
+        src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, inv_tw, inv_th, bands, nchunks, luts);
+}
+
+void launch_clahe(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,
+                  int64_t dst_stride, int W, int H, int n_streams, uint8_t* luts, cudaStream_t st,
+                  int64_t* launches) {
+    launch_clahe_lut_only(src, src_pitch, src_stride, W, H, n_streams, luts, st);
+    launch_clahe_apply_only(src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, n_streams, luts, st);
+    if (launches) *launches += 2;
 }
 
 void launch_copy_image(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,

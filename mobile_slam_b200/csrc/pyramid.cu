@@ -4,77 +4,132 @@
 // /root/reference/src/frontend/feature_tracker.cpp:123 (spec: SURVEY.md S2).  The Scharr derivative
 // images the reference also stores (4 B/px) are never materialised: the LK kernel derives them
 // from the staged u8 tile (lk.cu), which removes 4P bytes of writes and the matching reads per frame.
+//
+// Layout of the work: one warp walks down a strip of the destination level.  Per source row every lane
+// loads 8 consecutive source pixels with one 64-bit load (256 coalesced bytes per warp), gets the two
+// pixels to its left and the one to its right from its neighbour lanes by shuffle, and forms its four
+// horizontal 5-tap sums with DP4A; the vertical 5-tap runs over a register window of the last five
+// horizontal rows.  Each lane writes 4 destination pixels per row with one 32-bit store.  Every source
+// byte is read from HBM/L2 once (the 3 halo rows per strip come from L2) and nothing is staged in
+// shared memory.
 #include "kernels.h"
 
 namespace vs {
 
-constexpr int kTileW = 64;   // output tile width
-constexpr int kTileH = 16;   // output tile height
-constexpr int kSrcW = 2 * kTileW + 3;   // 131
-constexpr int kSrcH = 2 * kTileH + 3;   // 35
-constexpr int kSrcPitch = 144;          // bytes, multiple of 16
+constexpr int kPdWarps = 4;        // warps per CTA, each owns one strip
+constexpr int kPdLanes = 30;       // productive lanes per warp (lanes 0 and 31 only feed their neighbours)
+constexpr int kPdRows = 32;        // destination rows per strip
 
-__global__ void __launch_bounds__(256) pyr_down_kernel(const uint8_t* __restrict__ src, int sw, int sh,
-                                                       int spitch, uint8_t* __restrict__ dst, int dw, int dh,
-                                                       int dpitch, int64_t stream_stride) {
-    __shared__ __align__(16) uint8_t s_src[kSrcH * kSrcPitch];
-    __shared__ __align__(16) uint16_t s_h[kSrcH * kTileW];
-    const int tid = threadIdx.x;
-    const int s = blockIdx.z;
+__device__ __forceinline__ int dp4a_uu(unsigned a, unsigned b, int c) {
+    int d;
+    asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+__global__ void __launch_bounds__(32 * kPdWarps) pyr_down_kernel(const uint8_t* __restrict__ src, int sw, int sh,
+                                                                 int spitch, uint8_t* __restrict__ dst, int dw, int dh,
+                                                                 int dpitch, int64_t stream_stride, int nx, int ny,
+                                                                 int groups_per_strip) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int strip = blockIdx.x * kPdWarps + warp;
+    if (strip >= nx * ny) return;
+    const int ix = strip % nx, iy = strip / nx;
+    const int s = blockIdx.y;
     const uint8_t* img = src + (int64_t)s * stream_stride;
     uint8_t* out = dst + (int64_t)s * stream_stride;
-    const int ox0 = blockIdx.x * kTileW, oy0 = blockIdx.y * kTileH;
-    const int sx0 = 2 * ox0 - 2, sy0 = 2 * oy0 - 2;
+    const unsigned full = 0xffffffffu;
 
-    const bool interior = (sx0 >= 0) && (sy0 >= 0) && (sx0 + kSrcPitch <= spitch) && (sy0 + kSrcH <= sh) &&
-                          (sx0 + kSrcW <= sw);
-    if (interior) {
-        // sx0 = 128*bx - 2: read from the 16-byte aligned address 2 bytes... keep it simple: 4-byte
-        // words starting at sx0 - 2 (aligned because sx0 = 2 (mod 4)) shifted into place.
-        const int wq = (kSrcW + 2 + 3) / 4;   // words covering [sx0-2, sx0+kSrcW)
-        for (int idx = tid; idx < kSrcH * wq; idx += 256) {
-            const int r = idx / wq, q = idx - r * wq;
-            const uint8_t* p = img + (int64_t)(sy0 + r) * spitch + (sx0 - 2) + 4 * q;
-            const uint32_t v = *reinterpret_cast<const uint32_t*>(p);
-            // destination column of byte 0 of this word is 4q-2
-            const int c = 4 * q - 2;
-            uint8_t* d = s_src + r * kSrcPitch;
-            if (c >= 0) d[c] = (uint8_t)v;
-            if (c + 1 >= 0) d[c + 1] = (uint8_t)(v >> 8);
-            d[c + 2] = (uint8_t)(v >> 16);
-            d[c + 3] = (uint8_t)(v >> 24);
-        }
-    } else {
-        for (int idx = tid; idx < kSrcH * kSrcW; idx += 256) {
-            const int r = idx / kSrcW, c = idx - r * kSrcW;
-            const int gy = reflect101(sy0 + r, sh), gx = reflect101(sx0 + c, sw);
-            s_src[r * kSrcPitch + c] = img[(int64_t)gy * spitch + gx];
-        }
-    }
-    __syncthreads();
-    // horizontal 5-tap at even columns: h(r, x) = s(2x) + 4 s(2x+1) + 6 s(2x+2) + 4 s(2x+3) + s(2x+4)
-    for (int idx = tid; idx < kSrcH * kTileW; idx += 256) {
-        const int r = idx / kTileW, x = idx - r * kTileW;
-        const uint8_t* p = s_src + r * kSrcPitch + 2 * x;
-        s_h[idx] = (uint16_t)(p[0] + 4 * (p[1] + p[3]) + 6 * p[2] + p[4]);
-    }
-    __syncthreads();
-    // vertical 5-tap, 4 outputs per thread -> one 32-bit store
-    {
-        const int y = tid >> 4, x = (tid & 15) << 2;
-        const int oy = oy0 + y, ox = ox0 + x;
-        if (oy < dh && ox < dw) {
-            uint32_t packed = 0;
+    // lane l owns destination pixels 4*g .. 4*g+3 with g = ix*groups_per_strip + l - 1, i.e. source
+    // pixels 8*g .. 8*g+7; lanes 0 / 31 (and those past the strip) only supply neighbours
+    const int g = ix * groups_per_strip + lane - 1;
+    const int ngroups = (dw + 3) >> 2;
+    const bool productive = lane >= 1 && lane <= groups_per_strip && g < ngroups;
+    const int sx0 = 8 * g;
+    // a lane can use the aligned 64-bit load when its 8 pixels are inside the row; it can take its right
+    // neighbour's pixels by shuffle when that lane's 8 pixels are inside too
+    const bool inside = sx0 >= 0 && sx0 + 8 <= sw;
+    const bool left_edge = (sx0 == 0);                                // s(-2), s(-1) by reflection
+    const bool generic = productive && !(inside && sx0 + 16 <= sw);   // taps reach the right border
+    const int y0 = iy * kPdRows;
+    const int y1 = min(y0 + kPdRows, dh);
+
+    // raw 8 source pixels of one source row (issued early so that several rows are in flight per warp)
+    auto fetch = [&](int sy) -> uint2 {
+        if (!inside) return make_uint2(0u, 0u);
+        return __ldg(reinterpret_cast<const uint2*>(img + (int64_t)reflect101(sy, sh) * spitch + sx0));
+    };
+    // horizontal 5-tap sums of one source row for this lane's four destination pixels
+    auto hrow = [&](int sy, uint2 raw, int (&h)[4]) {
+        uint32_t lo = raw.x, hi = raw.y;
+        uint32_t lw = __shfl_up_sync(full, hi, 1);       // source pixels sx0-4 .. sx0-1
+        uint32_t rw = __shfl_down_sync(full, lo, 1);     // source pixels sx0+8 .. sx0+11
+        if (generic) {
+            // the lane(s) at the right border: REFLECT_101 byte loads for every tap
+            const uint8_t* row = img + (int64_t)reflect101(sy, sh) * spitch;
+            lo = hi = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const uint16_t* p = s_h + (2 * y) * kTileW + x + k;
-                const int v = p[0] + 4 * (p[kTileW] + p[3 * kTileW]) + 6 * p[2 * kTileW] + p[4 * kTileW];
-                packed |= (uint32_t)((v + 128) >> 8) << (8 * k);
+                lo |= (uint32_t)__ldg(row + reflect101(sx0 + k, sw)) << (8 * k);
+                hi |= (uint32_t)__ldg(row + reflect101(sx0 + 4 + k, sw)) << (8 * k);
             }
-            uint8_t* d = out + (int64_t)oy * dpitch + ox;
-            if (ox + 3 < dw) *reinterpret_cast<uint32_t*>(d) = packed;
+            rw = (uint32_t)__ldg(row + reflect101(sx0 + 8, sw));
+            lw = (uint32_t)__ldg(row + reflect101(sx0 - 2, sw)) << 16 | (uint32_t)__ldg(row + reflect101(sx0 - 1, sw)) << 24;
+        } else if (left_edge) {
+            lw = __byte_perm(lo, 0, 0x1200);             // (.., .., s(2), s(1)) in the two high bytes
+        }
+        // windows of 4 source pixels starting at sx0-2, sx0, sx0+2, sx0+4 (taps 1 4 6 4) and the 5th tap
+        const uint32_t wm2 = __funnelshift_r(lw, lo, 16), w2 = __funnelshift_r(lo, hi, 16), w6 = __funnelshift_r(hi, rw, 16);
+        const unsigned C = 0x04060401u, ONE = 0x00000001u;
+        h[0] = dp4a_uu(w2, ONE, dp4a_uu(wm2, C, 0));
+        h[1] = dp4a_uu(hi, ONE, dp4a_uu(lo, C, 0));
+        h[2] = dp4a_uu(w6, ONE, dp4a_uu(w2, C, 0));
+        h[3] = dp4a_uu(rw, ONE, dp4a_uu(hi, C, 0));
+    };
+    auto emit = [&](int y, const int (&a)[4], const int (&b)[4], const int (&c)[4], const int (&d4)[4], const int (&e)[4]) {
+        uint32_t packed = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int v = a[k] + e[k] + 4 * (b[k] + d4[k]) + 6 * c[k];
+            packed |= (uint32_t)((v + 128) >> 8) << (8 * k);
+        }
+        if (productive && y < y1) {
+            uint8_t* d = out + (int64_t)y * dpitch + 4 * g;
+            if (4 * g + 3 < dw) *reinterpret_cast<uint32_t*>(d) = packed;
             else
-                for (int k = 0; k < 4 && ox + k < dw; ++k) d[k] = (uint8_t)(packed >> (8 * k));
+                for (int k = 0; k < 4 && 4 * g + k < dw; ++k) d[k] = (uint8_t)(packed >> (8 * k));
+        }
+    };
+
+    int h0[4], h1[4], h2[4], h3[4], h4[4], h5[4], h6[4], h7[4], h8[4], h9[4], h10[4];
+    {
+        const uint2 r0 = fetch(2 * y0 - 2), r1 = fetch(2 * y0 - 1), r2 = fetch(2 * y0);
+        hrow(2 * y0 - 2, r0, h0);
+        hrow(2 * y0 - 1, r1, h1);
+        hrow(2 * y0, r2, h2);
+    }
+    // four destination rows (eight source rows in flight) per trip
+#pragma unroll 1
+    for (int y = y0; y < y1; y += 4) {
+        const int sy = 2 * y;
+        const uint2 r3 = fetch(sy + 1), r4 = fetch(sy + 2), r5 = fetch(sy + 3), r6 = fetch(sy + 4);
+        const uint2 r7 = fetch(sy + 5), r8 = fetch(sy + 6), r9 = fetch(sy + 7), r10 = fetch(sy + 8);
+        hrow(sy + 1, r3, h3);
+        hrow(sy + 2, r4, h4);
+        emit(y, h0, h1, h2, h3, h4);
+        hrow(sy + 3, r5, h5);
+        hrow(sy + 4, r6, h6);
+        emit(y + 1, h2, h3, h4, h5, h6);
+        hrow(sy + 5, r7, h7);
+        hrow(sy + 6, r8, h8);
+        emit(y + 2, h4, h5, h6, h7, h8);
+        hrow(sy + 7, r9, h9);
+        hrow(sy + 8, r10, h10);
+        emit(y + 3, h6, h7, h8, h9, h10);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            h0[k] = h8[k];
+            h1[k] = h9[k];
+            h2[k] = h10[k];
         }
     }
 }
@@ -83,10 +138,14 @@ void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from,
                      int64_t* launches) {
     const LevelDesc& a = pd.lv[level_from];
     const LevelDesc& b = pd.lv[level_from + 1];
-    dim3 grid((b.w + kTileW - 1) / kTileW, (b.h + kTileH - 1) / kTileH, n_streams);
-    pyr_down_kernel<<<grid, 256, 0, st>>>(pyr_base + a.offset, a.w, a.h, a.pitch,
-                                          const_cast<uint8_t*>(pyr_base) + b.offset, b.w, b.h, b.pitch,
-                                          pd.stream_bytes);
+    const int ngroups = (b.w + 3) / 4;
+    const int nx = (ngroups + kPdLanes - 1) / kPdLanes;
+    const int gps = (ngroups + nx - 1) / nx;
+    const int ny = (b.h + kPdRows - 1) / kPdRows;
+    dim3 grid((nx * ny + kPdWarps - 1) / kPdWarps, n_streams);
+    pyr_down_kernel<<<grid, 32 * kPdWarps, 0, st>>>(pyr_base + a.offset, a.w, a.h, a.pitch,
+                                                    const_cast<uint8_t*>(pyr_base) + b.offset, b.w, b.h, b.pitch,
+                                                    pd.stream_bytes, nx, ny, gps);
     if (launches) *launches += 1;
 }
 

@@ -42,28 +42,37 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict
     const int x0 = tx * tw, y0 = ty * th;
     const int xa = x0 & ~3, nw = ((x0 + tw - 1) >> 2) - (xa >> 2) + 1;
     uint32_t* mine = s_cnt + tid;
-    const int total = nw * th;
-    for (int idx0 = tid; idx0 < total; idx0 += 4 * NT) {
-        // four independent loads in flight per thread before the dependent shared-memory updates
+    // thread walks the tile's words in row-major order, NT apart: (y, q) advance incrementally
+    const int dq = NT % nw, dy = NT / nw;
+    int y = tid / nw, q = tid - y * nw;
+    const uint8_t* rowp = img + (int64_t)(y0 + y) * pitch + xa;
+    while (y < th) {
+        // up to four independent loads in flight per thread before the dependent shared-memory updates
         uint32_t v[4];
-        int k0[4], k1[4];
+        int lo[4], hi[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const int idx = idx0 + u * NT;
-            const int ic = min(idx, total - 1);
-            const int y = ic / nw, q = ic - y * nw;
+            const bool ok = y < th;
+            v[u] = ok ? __ldg(reinterpret_cast<const uint32_t*>(rowp) + q) : 0u;
             const int xw = xa + 4 * q;
-            v[u] = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)(y0 + y) * pitch + xw));
-            k0[u] = max(x0 - xw, 0);
-            k1[u] = idx < total ? min(x0 + tw - xw, 4) : 0;
+            lo[u] = ok ? max(x0 - xw, 0) : 4;              // valid bytes of this word: lo .. hi-1
+            hi[u] = min(x0 + tw - xw, 4);
+            q += dq;
+            y += dy;
+            rowp += (int64_t)dy * pitch;
+            if (q >= nw) {
+                q -= nw;
+                ++y;
+                rowp += pitch;
+            }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            uint32_t w = v[u] >> (8 * k0[u]);
-            for (int k = k0[u]; k < k1[u]; ++k) {
-                const uint32_t b = w & 255u;
-                w >>= 8;
-                mine[(b & 63u) * NT] += 1u << ((b >> 6) * 8);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t b = (v[u] >> (8 * k)) & 255u;
+                const uint32_t inc = (k >= lo[u] && k < hi[u]) ? (1u << ((b >> 3) & 0x18u)) : 0u;
+                mine[(b & 63u) * NT] += inc;
             }
         }
     }
@@ -224,8 +233,8 @@ __global__ void __launch_bounds__(256) clahe_lut_generic_kernel(const uint8_t* _
 // down the band, one aligned 32-bit word (4 pixels) per lane and row, with the per-column weights
 // held in registers.
 // ---------------------------------------------------------------------------------------------
-constexpr int kApplyThreads = 256;
-constexpr int kApplyMaxCells = 9;
+constexpr int kApplyCells = kClaheTiles + 1;   // interpolation cells per row: cx = -1 .. 7
+constexpr int kApplyRowSplit = 2;             // CTAs per band (each rebuilds the band's cell tables)
 
 struct ClaheBands {
     int start[kClaheTiles + 2];   // band b (cell row b-1) covers rows start[b] .. start[b+1]-1
@@ -235,27 +244,26 @@ __device__ __forceinline__ float round_magic(float r) {   // round-half-even of 
     return __fadd_rn(r, 12582912.0f);
 }
 
-__global__ void __launch_bounds__(kApplyThreads) clahe_apply_kernel(const uint8_t* __restrict__ src, int src_pitch,
-                                                                    int64_t src_stride, uint8_t* __restrict__ dst,
-                                                                    int dst_pitch, int64_t dst_stride, int W, int H,
-                                                                    float inv_tw, float inv_th, ClaheBands bands,
-                                                                    int nchunks, const uint8_t* __restrict__ luts) {
-    __shared__ __align__(16) uint2 s_cell[kApplyMaxCells][256];     // (p1, p2, q1, q2) as 4 x fp16
+// blockDim.x = 32 * (number of 128-column chunks): warp w owns columns 128w .. 128w+127 of the band
+__global__ void __launch_bounds__(1024) clahe_apply_kernel(const uint8_t* __restrict__ src, int src_pitch,
+                                                           int64_t src_stride, uint8_t* __restrict__ dst,
+                                                           int dst_pitch, int64_t dst_stride, int W, int H,
+                                                           float inv_tw, float inv_th, ClaheBands bands,
+                                                           const uint8_t* __restrict__ luts) {
+    __shared__ __align__(16) uint2 s_cell[kApplyCells][256];     // (p1, p2, q1, q2) as 4 x fp16
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int s = blockIdx.y;
-    const int band = blockIdx.x / nchunks, chunk = blockIdx.x - band * nchunks;
-    const int y_begin = bands.start[band], y_end = bands.start[band + 1];
+    const int band = blockIdx.x / kApplyRowSplit, part = blockIdx.x - band * kApplyRowSplit;
+    const int b0 = bands.start[band], b1 = bands.start[band + 1];
+    const int per = (b1 - b0 + kApplyRowSplit - 1) / kApplyRowSplit;
+    const int y_begin = b0 + part * per, y_end = min(y_begin + per, b1);
     if (y_begin >= y_end) return;
     const int cy = band - 1;                                         // cell row: tile rows (cy, cy+1) clamped
     const int ty1 = max(cy, 0), ty2 = min(cy + 1, kClaheTiles - 1);
-    const int xc0 = chunk * 128, xc1 = min(xc0 + 128, W) - 1;
-    const int cell_first = (int)floorf(__fsub_rn(__fmul_rn((float)xc0, inv_tw), 0.5f));
-    const int cell_last = (int)floorf(__fsub_rn(__fmul_rn((float)xc1, inv_tw), 0.5f));
-    const int ncell = cell_last - cell_first + 1;
     const uint8_t* L = luts + (int64_t)s * (kClaheTiles * kClaheTiles * 256);
-    for (int idx = tid; idx < ncell * 256; idx += kApplyThreads) {
+    for (int idx = tid; idx < kApplyCells * 256; idx += blockDim.x) {
         const int c = idx >> 8, v = idx & 255;
-        const int cx = cell_first + c;
+        const int cx = c - 1;
         const int tx1 = max(cx, 0), tx2 = min(cx + 1, kClaheTiles - 1);
         const __half2 top = __halves2half2(__ushort2half_rn(L[(ty1 * kClaheTiles + tx1) * 256 + v]),
                                            __ushort2half_rn(L[(ty1 * kClaheTiles + tx2) * 256 + v]));
@@ -263,20 +271,23 @@ __global__ void __launch_bounds__(kApplyThreads) clahe_apply_kernel(const uint8_
                                            __ushort2half_rn(L[(ty2 * kClaheTiles + tx2) * 256 + v]));
         s_cell[c][v] = make_uint2(*reinterpret_cast<const uint32_t*>(&top), *reinterpret_cast<const uint32_t*>(&bot));
     }
-    // per-lane column constants: word x = xc0 + 4*lane
-    const int x = xc0 + 4 * lane;
+    __syncthreads();
+    const int nchunks = (W + 127) >> 7, nwarps = blockDim.x >> 5;
+    const char* cells = reinterpret_cast<const char*>(&s_cell[0][0]);
+    for (int chunk = warp; chunk < nchunks; chunk += nwarps) {
+    // per-lane column constants: word x = 128*chunk + 4*lane
+    const int x = 128 * chunk + 4 * lane;
     float xa[4], xa1[4];
-    const uint2* cellp[4];
+    uint32_t cell_off[4];                                            // byte offset of the pixel's cell table
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float txf = __fsub_rn(__fmul_rn((float)(x + k), inv_tw), 0.5f);
         const int tx1r = (int)floorf(txf);
         xa[k] = __fsub_rn(txf, (float)tx1r);
         xa1[k] = __fsub_rn(1.0f, xa[k]);
-        cellp[k] = s_cell[min(max(tx1r - cell_first, 0), kApplyMaxCells - 1)];
+        cell_off[k] = (uint32_t)min(max(tx1r + 1, 0), kApplyCells - 1) * (256u * 8u);
     }
-    __syncthreads();
-    if (x >= W) return;
+    if (x >= W) continue;
     const uint8_t* img = src + (int64_t)s * src_stride + x;
     uint8_t* out = dst + (int64_t)s * dst_stride + x;
     const bool full = (x + 3 < W);
@@ -295,7 +306,7 @@ __global__ void __launch_bounds__(kApplyThreads) clahe_apply_kernel(const uint8_
         uint32_t o4 = 0;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const uint2 ent = cellp[k][(v4 >> (8 * k)) & 255u];
+            const uint2 ent = *reinterpret_cast<const uint2*>(cells + cell_off[k] + ((v4 >> (8 * k)) & 255u) * 8u);
             const float2 pt = __half22float2(*reinterpret_cast<const __half2*>(&ent.x));
             const float2 pb = __half22float2(*reinterpret_cast<const __half2*>(&ent.y));
             const float top = __fadd_rn(__fmul_rn(pt.x, xa1[k]), __fmul_rn(pt.y, xa[k]));
@@ -309,15 +320,15 @@ __global__ void __launch_bounds__(kApplyThreads) clahe_apply_kernel(const uint8_
         else
             for (int k = 0; k < 4 && x + k < W; ++k) dp[k] = (uint8_t)(o4 >> (8 * k));
     };
-    constexpr int RS = kApplyThreads / 32;       // row stride between a warp's rows
-    for (int y = y_begin + warp; y < y_end; y += 4 * RS) {
-        // four rows in flight per lane before the dependent LUT lookups
-        const uint32_t a0 = fetch(y), a1 = fetch(y + RS), a2 = fetch(y + 2 * RS), a3 = fetch(y + 3 * RS);
+    for (int y = y_begin; y < y_end; y += 4) {
+        // four rows in flight per lane before the dependent table lookups
+        const uint32_t a0 = fetch(y), a1 = fetch(y + 1), a2 = fetch(y + 2), a3 = fetch(y + 3);
         process(y, a0);
-        process(y + RS, a1);
-        process(y + 2 * RS, a2);
-        process(y + 3 * RS, a3);
+        process(y + 1, a1);
+        process(y + 2, a2);
+        process(y + 3, a3);
     }
+    }   // chunk
 }
 
 // plain strided copy used when equalize == 0 (level 0 = the raw frame)
@@ -399,8 +410,9 @@ void launch_clahe_apply_only(const uint8_t* src, int src_pitch, int64_t src_stri
     }
     while (b < kClaheTiles + 1) bands.start[++b] = H;
     const int nchunks = (W + 127) / 128;
-    clahe_apply_kernel<<<dim3((kClaheTiles + 1) * nchunks, n_streams), kApplyThreads, 0, st>>>(
-        src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, inv_tw, inv_th, bands, nchunks, luts);
+    const int nwarps = nchunks < 32 ? nchunks : 32;
+    clahe_apply_kernel<<<dim3((kClaheTiles + 1) * kApplyRowSplit, n_streams), 32 * nwarps, 0, st>>>(
+        src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, inv_tw, inv_th, bands, luts);
 }
 
 void launch_clahe(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,

@@ -18,7 +18,6 @@ namespace vs {
 
 constexpr int kPdWarps = 4;        // warps per CTA, each owns one strip
 constexpr int kPdLanes = 30;       // productive lanes per warp (lanes 0 and 31 only feed their neighbours)
-constexpr int kPdRows = 32;        // destination rows per strip
 
 __device__ __forceinline__ int dp4a_uu(unsigned a, unsigned b, int c) {
     int d;
@@ -29,7 +28,7 @@ __device__ __forceinline__ int dp4a_uu(unsigned a, unsigned b, int c) {
 __global__ void __launch_bounds__(32 * kPdWarps) pyr_down_kernel(const uint8_t* __restrict__ src, int sw, int sh,
                                                                  int spitch, uint8_t* __restrict__ dst, int dw, int dh,
                                                                  int dpitch, int64_t stream_stride, int nx, int ny,
-                                                                 int groups_per_strip) {
+                                                                 int groups_per_strip, int rows_per_strip) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int strip = blockIdx.x * kPdWarps + warp;
     if (strip >= nx * ny) return;
@@ -50,8 +49,8 @@ __global__ void __launch_bounds__(32 * kPdWarps) pyr_down_kernel(const uint8_t* 
     const bool inside = sx0 >= 0 && sx0 + 8 <= sw;
     const bool left_edge = (sx0 == 0);                                // s(-2), s(-1) by reflection
     const bool generic = productive && !(inside && sx0 + 16 <= sw);   // taps reach the right border
-    const int y0 = iy * kPdRows;
-    const int y1 = min(y0 + kPdRows, dh);
+    const int y0 = iy * rows_per_strip;
+    const int y1 = min(y0 + rows_per_strip, dh);
 
     // raw 8 source pixels of one source row (issued early so that several rows are in flight per warp)
     auto fetch = [&](int sy) -> uint2 {
@@ -141,11 +140,13 @@ void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from,
     const int ngroups = (b.w + 3) / 4;
     const int nx = (ngroups + kPdLanes - 1) / kPdLanes;
     const int gps = (ngroups + nx - 1) / nx;
-    const int ny = (b.h + kPdRows - 1) / kPdRows;
+    // short strips on the small levels (more warps, shorter dependent chains); each strip re-reads 3 source rows
+    const int rows = b.h >= 192 ? 16 : 8;
+    const int ny = (b.h + rows - 1) / rows;
     dim3 grid((nx * ny + kPdWarps - 1) / kPdWarps, n_streams);
     pyr_down_kernel<<<grid, 32 * kPdWarps, 0, st>>>(pyr_base + a.offset, a.w, a.h, a.pitch,
                                                     const_cast<uint8_t*>(pyr_base) + b.offset, b.w, b.h, b.pitch,
-                                                    pd.stream_bytes, nx, ny, gps);
+                                                    pd.stream_bytes, nx, ny, gps, rows);
     if (launches) *launches += 1;
 }
 

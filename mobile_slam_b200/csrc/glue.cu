@@ -111,15 +111,41 @@ __global__ void __launch_bounds__(256) post_lk_kernel(GlueParams g) {
 // ---------------------------------------------------------------------------------------------
 // setMask: order by track_cnt (exact libstdc++ std::sort moves), greedy keep outside painted discs
 // ---------------------------------------------------------------------------------------------
-int set_mask_smem_bytes(int cap) { return cap * (4 + 4 + 4 + 4 + 4); }
+static __host__ __device__ inline int pow2_at_least(int n) {
+    int p = 1;
+    while (p < n) p <<= 1;
+    return p;
+}
+int set_mask_smem_bytes(int cap) { return pow2_at_least(cap) * 8 + cap * (4 + 4 + 4 + 4 + 4 + 4 + 4); }
+
+__device__ __forceinline__ void bitonic_sort_desc_u64(unsigned long long* v, int N, int tid, int nthreads) {
+    for (int k = 2; k <= N; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (N >> 1); t += nthreads) {
+                const int i = 2 * j * (t / j) + (t % j);
+                const int l = i + j;
+                const unsigned long long a = v[i], b = v[l];
+                const bool desc = (i & k) == 0;
+                if ((a < b) == desc) {
+                    v[i] = b;
+                    v[l] = a;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
 
 __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
     extern __shared__ __align__(16) uint8_t dsm[];
-    int* src = reinterpret_cast<int*>(dsm);          // surviving work indices (order preserved)
+    unsigned long long* ck = reinterpret_cast<unsigned long long*>(dsm);   // (key, position) sort keys
+    int* src = reinterpret_cast<int*>(ck + pow2_at_least(g.cap));          // surviving work indices (order preserved)
     int* key = src + g.cap;                          // track_cnt of src[j]
     int* perm = key + g.cap;                         // sorted order (indices into src)
     int* kidx = perm + g.cap;                        // kept work indices
-    short2* acc = reinterpret_cast<short2*>(kidx + g.cap);   // kept rounded centres
+    int* lpos = kidx + g.cap;                        // partition stop lists
+    int* rpos = lpos + g.cap;
+    short2* acc = reinterpret_cast<short2*>(rpos + g.cap);   // kept rounded centres
     __shared__ int s_warp_cnt[8];
     __shared__ int s_kn;
     const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
@@ -138,7 +164,20 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
         }
     }
     __syncthreads();
-    if (tid == 0) std_sort_indices(perm, n2, DescByKey{key});
+    // std::sort(track_cnt desc) with libstdc++'s exact tie order: introsort partition phase on one warp,
+    // then its final insertion sort == a stable sort of what the partitions left (introsort.cuh)
+    if (tid < 32) warp_introsort_loop_desc(perm, key, n2, lpos, rpos, lane);
+    __syncthreads();
+    {
+        const int N = pow2_at_least(n2);
+        for (int i = tid; i < N; i += 256)
+            ck[i] = i < n2 ? ((unsigned long long)(unsigned int)key[perm[i]] << 32) |
+                                 ((unsigned long long)(0xFFFFu - (unsigned int)i) << 16) | (unsigned int)perm[i]
+                           : 0ull;
+        __syncthreads();
+        bitonic_sort_desc_u64(ck, N, tid, 256);
+        for (int i = tid; i < n2; i += 256) perm[i] = (int)(ck[i] & 0xFFFFull);
+    }
     __syncthreads();
     if (tid < 32) {
         const int R = g.min_dist;

@@ -167,4 +167,93 @@ __host__ __device__ inline void std_sort_indices(int* v, int n, Comp comp) {
     }
 }
 
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------------------------------------
+// Warp-cooperative version of the __introsort_loop phase of std_sort_indices (same element moves).
+//
+// __unguarded_partition only ever looks at each element's ORIGINAL key: the left cursor stops at
+// the k-th element (ascending) with !comp(e, pivot), the right cursor at the k-th element
+// (descending) with !comp(pivot, e), and pair k is swapped while left < right.  Both stop lists are
+// built with ballots, the first crossing pair K is found, pairs 0..K-1 are swapped in parallel, and
+//   cut = min(Lpos[K], Rpos[K-1])
+// (the left cursor cannot pass the slot the previous swap filled with an element it stops at).
+// After this phase libstdc++ runs __final_insertion_sort, which is a STABLE sort of what the loop
+// left behind; the caller does that with a parallel sort on (key, position).
+// Call with all 32 lanes of one warp; v / key / lpos / rpos live in shared memory.
+// ---------------------------------------------------------------------------------------------
+__device__ inline void warp_introsort_loop_desc(int* v, const int* key, int n, int* lpos, int* rpos, int lane) {
+    const unsigned full = 0xffffffffu;
+    if (n <= 16) return;
+    int lg = 0;
+    for (int t = n; t > 1; t >>= 1) ++lg;
+    // explicit stack in registers of lane-uniform values (depth <= 2*lg <= 64 entries is never reached:
+    // every push is matched by shrinking the current range, so 64 slots suffice as in the serial version)
+    int stack_first[64], stack_last[64], stack_depth[64];
+    int sp = 1;
+    stack_first[0] = 0; stack_last[0] = n; stack_depth[0] = 2 * lg;
+    DescByKey comp{key};
+    while (sp > 0) {
+        --sp;
+        int first = stack_first[sp], last = stack_last[sp], depth = stack_depth[sp];
+        while (last - first > 16) {
+            if (depth == 0) {
+                if (lane == 0) iso_heap_sort(v, first, last, comp);
+                __syncwarp();
+                last = first;
+                break;
+            }
+            --depth;
+            const int mid = first + (last - first) / 2;
+            if (lane == 0) iso_move_median_to_first(v, first, first + 1, mid, last - 1, comp);
+            __syncwarp();
+            const int pk = key[v[first]];
+            const int lo = first + 1;
+            // left stops: key <= pivot key, ascending positions
+            int nL = 0;
+            for (int i0 = lo; i0 < last; i0 += 32) {
+                const int i = i0 + lane;
+                const bool a = i < last && key[v[i]] <= pk;
+                const unsigned bal = __ballot_sync(full, a);
+                if (a) lpos[nL + __popc(bal & ((1u << lane) - 1u))] = i;
+                nL += __popc(bal);
+            }
+            // right stops: key >= pivot key, descending positions
+            int nR = 0;
+            for (int i0 = last - 1; i0 >= lo; i0 -= 32) {
+                const int i = i0 - lane;
+                const bool b = i >= lo && key[v[i]] >= pk;
+                const unsigned bal = __ballot_sync(full, b);
+                if (b) rpos[nR + __popc(bal & ((1u << lane) - 1u))] = i;
+                nR += __popc(bal);
+            }
+            __syncwarp();
+            const int nmin = nL < nR ? nL : nR;
+            int K = nmin;
+            for (int k0 = 0; k0 < nmin; k0 += 32) {
+                const int k = k0 + lane;
+                const bool cross = k < nmin && lpos[k] >= rpos[k];
+                const unsigned bal = __ballot_sync(full, cross);
+                if (bal) {
+                    K = k0 + __ffs(bal) - 1;
+                    break;
+                }
+            }
+            int cut = last;
+            if (K < nL) cut = lpos[K];
+            if (K >= 1 && rpos[K - 1] < cut) cut = rpos[K - 1];
+            for (int k = lane; k < K; k += 32) {
+                const int a = lpos[k], b = rpos[k];
+                const int t = v[a];
+                v[a] = v[b];
+                v[b] = t;
+            }
+            __syncwarp();
+            stack_first[sp] = cut; stack_last[sp] = last; stack_depth[sp] = depth; ++sp;
+            last = cut;
+        }
+    }
+}
+#endif  // __CUDACC__
+
 }  // namespace vs

@@ -265,7 +265,7 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     int cap = cfg->capacity > 0 ? cfg->capacity : (cfg->max_cnt > 256 ? cfg->max_cnt : 256);
     if (cap < cfg->max_cnt) cap = cfg->max_cnt;
     cap = round_up(cap, 32);
-    if (cap > 32768) { delete t; set_error("capacity too large"); return VS_ERR_CAPACITY; }
+    if (cap > 4096) { delete t; set_error("capacity above 4096 features per stream is not supported"); return VS_ERR_CAPACITY; }
     t->cap = cap;
     t->cfg.capacity = cap;
     t->n_bound = cfg->max_cnt;

@@ -116,6 +116,7 @@ static __host__ __device__ inline int pow2_at_least(int n) {
     while (p < n) p <<= 1;
     return p;
 }
+constexpr int kFixedPointMax = 768;   // above this the greedy keep runs warp-serial
 int set_mask_smem_bytes(int cap) { return pow2_at_least(cap) * 8 + cap * (4 + 4 + 4 + 4 + 4 + 4 + 4); }
 
 __device__ __forceinline__ void bitonic_sort_desc_u64(unsigned long long* v, int N, int tid, int nthreads) {
@@ -179,7 +180,59 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
         for (int i = tid; i < n2; i += 256) perm[i] = (int)(ck[i] & 0xFFFFull);
     }
     __syncthreads();
-    if (tid < 32) {
+    if (n2 <= kFixedPointMax) {
+        // Greedy keep (feature_tracker.cpp:79-86) as a fixed point: kept[q] = base(q) && no kept a < q whose
+        // disc covers q.  The recurrence is triangular, so Jacobi sweeps from "all base-ok points kept"
+        // reach its unique solution — the sequential result — after (longest rejection chain + 1) sweeps.
+        const int R = g.min_dist;
+        int* cur = lpos;
+        int* nxt = rpos;
+        for (int q = tid; q < n2; q += 256) {
+            const float2 p = g.w_next[o + src[perm[q]]];
+            const int rx = cv_round(p.x), ry = cv_round(p.y);
+            acc[q] = make_short2((short)rx, (short)ry);
+            cur[q] = g.base_mask[(int64_t)ry * g.mask_pitch + rx] == 255;
+            kidx[q] = cur[q];                        // base-ok flag, fixed
+        }
+        __syncthreads();
+        for (int sweep = 0; sweep <= n2; ++sweep) {
+            int changed = 0;
+            for (int q = tid; q < n2; q += 256) {
+                int k = kidx[q];
+                if (k) {
+                    const int rx = acc[q].x, ry = acc[q].y;
+                    for (int a = 0; a < q; ++a) {
+                        if (!cur[a]) continue;
+                        const int dy = abs(ry - (int)acc[a].y), dx = abs(rx - (int)acc[a].x);
+                        if (dy <= R && dx <= g.disc_hw[dy]) {
+                            k = 0;
+                            break;
+                        }
+                    }
+                }
+                nxt[q] = k;
+                changed |= (k != cur[q]);
+            }
+            const int any = __syncthreads_or(changed);
+            int* t = cur;
+            cur = nxt;
+            nxt = t;
+            if (!any) break;
+        }
+        // ordered compaction of the kept points
+        int base = 0;
+        for (int chunk = 0; chunk < n2; chunk += 256) {
+            const int q = chunk + tid;
+            const bool ok = q < n2 && cur[q];
+            const int widx = q < n2 ? src[perm[q]] : 0;
+            __syncthreads();                         // kidx is about to be reused as the kept list
+            const int slot = block_compact_slot(ok, tid, s_warp_cnt, base);
+            if (slot >= 0) nxt[slot] = widx;
+        }
+        __syncthreads();
+        for (int j = tid; j < base; j += 256) kidx[j] = nxt[j];
+        if (tid == 0) s_kn = base;
+    } else if (tid < 32) {
         const int R = g.min_dist;
         int A = 0;
         for (int q0 = 0; q0 < n2; q0 += 32) {

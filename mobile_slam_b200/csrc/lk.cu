@@ -241,21 +241,55 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
     return d;
 }
 
-// stage nrows x nwords aligned words of a level into the warp's tile; x0 is a multiple of 4
+// stage NROWS x NWORDS aligned words of a level into the warp's tile; x0 is a multiple of 4.
+// Fully unrolled: when the tile lies inside the level (the common case, warp-uniform test) a lane issues
+// all of its loads back to back before the first shared-memory store, so 6..9 requests are in flight.
+template <int NROWS, int NWORDS>
 __device__ __forceinline__ void stage_words(uint32_t* tile, const uint8_t* __restrict__ img, int w, int h, int pitch,
-                                            int x0, int y0, int nrows, int nwords, int lane) {
-    for (int idx = lane; idx < nrows * nwords; idx += 32) {
-        const int r = idx / nwords, q = idx - r * nwords;
-        const int gx = x0 + 4 * q, gy = y0 + r;
-        uint32_t v;
-        if (gy >= 0 && gy < h && gx >= 0 && gx + 3 < w) {
-            v = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)gy * pitch + gx));
-        } else {
-            const uint8_t* row = img + (int64_t)reflect101(gy, h) * pitch;
-            v = (uint32_t)__ldg(row + reflect101(gx, w)) | ((uint32_t)__ldg(row + reflect101(gx + 1, w)) << 8) |
-                ((uint32_t)__ldg(row + reflect101(gx + 2, w)) << 16) | ((uint32_t)__ldg(row + reflect101(gx + 3, w)) << 24);
+                                            int x0, int y0, int lane) {
+    constexpr int TOTAL = NROWS * NWORDS, U = (TOTAL + 31) / 32;
+    constexpr int DR = 32 / NWORDS, DQ = 32 % NWORDS;
+    int r = lane / NWORDS, q = lane - r * NWORDS;
+    const bool interior = x0 >= 0 && y0 >= 0 && x0 + 4 * NWORDS <= w && y0 + NROWS <= h;
+    if (interior) {
+        const uint8_t* base = img + (int64_t)y0 * pitch + x0;
+        uint32_t v[U];
+        int off[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const bool ok = (u < U - 1) || (lane + 32 * u < TOTAL);
+            off[u] = r * (kFastPitch / 4) + q;
+            v[u] = ok ? __ldg(reinterpret_cast<const uint32_t*>(base + (int64_t)r * pitch) + q) : 0u;
+            r += DR;
+            q += DQ;
+            if (q >= NWORDS) {
+                q -= NWORDS;
+                ++r;
+            }
         }
-        tile[r * (kFastPitch / 4) + q] = v;
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if ((u < U - 1) || (lane + 32 * u < TOTAL)) tile[off[u]] = v[u];
+    } else {
+#pragma unroll 1
+        for (int idx = lane; idx < TOTAL; idx += 32) {
+            const int gx = x0 + 4 * q, gy = y0 + r;
+            uint32_t v;
+            if (gy >= 0 && gy < h && gx >= 0 && gx + 3 < w) {
+                v = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)gy * pitch + gx));
+            } else {
+                const uint8_t* row = img + (int64_t)reflect101(gy, h) * pitch;
+                v = (uint32_t)__ldg(row + reflect101(gx, w)) | ((uint32_t)__ldg(row + reflect101(gx + 1, w)) << 8) |
+                    ((uint32_t)__ldg(row + reflect101(gx + 2, w)) << 16) | ((uint32_t)__ldg(row + reflect101(gx + 3, w)) << 24);
+            }
+            tile[r * (kFastPitch / 4) + q] = v;
+            r += DR;
+            q += DQ;
+            if (q >= NWORDS) {
+                q -= NWORDS;
+                ++r;
+            }
+        }
     }
 }
 
@@ -323,7 +357,7 @@ __global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_fast21_kernel(LkParams
         // ---- template: tile origin (x aligned down to 4, ipy - 1), 24 rows x 8 words ----
         const int tx0 = (ipx - 1) & ~3, ax = (ipx - 1) - tx0;
         __syncwarp();
-        stage_words(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, WIN + 3, 8, lane);
+        stage_words<WIN + 3, 8>(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, lane);
         __syncwarp();
         const bool border = ipx < 0 || ipy < 0 || ipx + WIN + 1 > L.w || ipy + WIN + 1 > L.h;
         int s11 = 0, s12 = 0, s22 = 0;
@@ -416,7 +450,7 @@ __global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_fast21_kernel(LkParams
                 tox = (iqx - kLkMargin) & ~3;
                 toy = iqy - kLkMargin;
                 __syncwarp();
-                stage_words(tile, J, L.w, L.h, L.pitch, tox, toy, kFastRows, kFastPitch / 4, lane);
+                stage_words<kFastRows, kFastPitch / 4>(tile, J, L.w, L.h, L.pitch, tox, toy, lane);
                 __syncwarp();
                 staged = true;
             }

@@ -32,6 +32,9 @@ extern "C" {
 #define VS_API
 #endif
 
+struct vs_tracker;              /* opaque handle */
+typedef struct vs_tracker vs_tracker;
+
 typedef enum vs_status {
     VS_OK = 0,
     VS_ERR_INVALID = -1,   /* bad argument / config           */

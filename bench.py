@@ -323,6 +323,7 @@ def workload_config(args, cfg, streams):
         "workload": f"{args.config}: {cfg['width']}x{cfg['height']} mono, max_cnt {cfg['max_cnt']}, min_dist {cfg['min_dist']}, "
                     f"LK win {LK_WIN} maxLevel {cfg['max_level']} ({len(lv)} levels), camera {cfg['model']}",
         "streams_per_gpu": streams, "ransac": "device" if args.ransac else "off (both arms)",
+        "e2e_pipeline_lanes": args.lanes,
         "parallelism": f"stream-sharded x{args.gpus}, no collective",
     }
 
@@ -386,6 +387,7 @@ def run_ours(args, rank, world, local_rank):
         return (C.c_double * S)(*([0.05 * i] * S))
 
     # ---- (1) device-resident throughput: CUDA events on the handle's own stream ----
+    tc.pipeline_lanes = args.dev_lanes
     bt = BatchTracker(tc, cam, S)
     ext = torch.cuda.ExternalStream(bt.cuda_stream, device=dev)
     step = 0
@@ -418,7 +420,12 @@ def run_ours(args, rank, world, local_rank):
     prof = bt.profile()
     bt.set_profiling(False)
 
-    # ---- (3) end to end through the C ABI with host frames ----
+    # ---- (3) end to end through the C ABI with host frames: the handle is split into pipeline lanes so the H2D copy
+    #          of one lane's frames overlaps the kernels of another (all inside the one synchronous call) ----
+    bt.close()
+    tc.pipeline_lanes = args.lanes
+    bt = BatchTracker(tc, cam, S)
+    step = 0
     for _ in range(Wm):
         bt.track_pinned(h_frames[bounce(step, n_buf)].data_ptr(), H * W, times(step))
         step += 1
@@ -547,6 +554,8 @@ def main():
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--streams", type=int, default=256, help="camera streams per GPU")
     ap.add_argument("--ransac", type=int, default=0)
+    ap.add_argument("--lanes", type=int, default=4, help="pipeline lanes of the e2e (host-frame) handle")
+    ap.add_argument("--dev-lanes", type=int, default=1, help="pipeline lanes of the device-resident handle")
     ap.add_argument("--max-frames", type=int, default=32, help="distinct frames buffered per stream")
     ap.add_argument("--latency-frames", type=int, default=200)
     ap.add_argument("--cpu-frames", type=int, default=60, help="cpu_baseline sample: frames per process")

@@ -89,6 +89,8 @@ typedef struct vs_tracker_config {
     const uint8_t* fisheye_mask_image; /* optional H x W mask (255 = keep), replaces the auto circle; may be NULL */
     int32_t fisheye_mask_stride;
     int32_t first_feature_id;   /* initial value of the per-stream n_id counter (0) */
+    int32_t pipeline_lanes;     /* >1: split the handle's streams into that many lanes, each on its own CUDA stream, so
+                                   the host->device copy of one lane overlaps the kernels of another (0/1 = one lane) */
     vs_camera camera;
 } vs_tracker_config;
 

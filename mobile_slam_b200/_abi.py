@@ -33,7 +33,7 @@ class VsTrackerConfig(C.Structure):
                 ("lk_iterations", C.c_int32), ("lk_eps", C.c_double), ("fb_check", C.c_int32),
                 ("fb_threshold", C.c_double), ("ransac_mode", C.c_int32), ("capacity", C.c_int32),
                 ("fisheye_mask_image", C.c_void_p), ("fisheye_mask_stride", C.c_int32),
-                ("first_feature_id", C.c_int32), ("camera", VsCamera)]
+                ("first_feature_id", C.c_int32), ("pipeline_lanes", C.c_int32), ("camera", VsCamera)]
 
 
 class VsTrackResult(C.Structure):

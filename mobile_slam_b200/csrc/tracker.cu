@@ -209,6 +209,7 @@ void vs_tracker_default_config(vs_tracker_config* c) {
     c->fb_check = 0;
     c->fb_threshold = 0.5;
     c->ransac_mode = VS_RANSAC_DEVICE;
+    c->pipeline_lanes = 0;
     c->camera.model_type = VS_CAM_PINHOLE;
     c->camera.width = 752;
     c->camera.height = 480;
@@ -268,6 +269,40 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     if (cap > 4096) { delete t; set_error("capacity above 4096 features per stream is not supported"); return VS_ERR_CAPACITY; }
     t->cap = cap;
     t->cfg.capacity = cap;
+
+    // ---- pipeline lanes: the handle becomes a fork/join point over sub-handles, one CUDA stream each ----
+    int n_lanes = cfg->pipeline_lanes;
+    if (n_lanes > cfg->n_streams) n_lanes = cfg->n_streams;
+    if (cfg->ransac_mode == VS_RANSAC_CALLBACK) n_lanes = 1;     // the callback hop is a per-handle host sync
+    if (n_lanes > 1) {
+        t->cfg.pipeline_lanes = n_lanes;
+        cudaError_t e = cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreate(&t->ev0);
+        if (e == cudaSuccess) e = cudaEventCreate(&t->ev1);
+        if (e != cudaSuccess) { set_error("lane fork/join setup: %s", cudaGetErrorString(e)); vs_tracker_destroy(t); return VS_ERR_CUDA; }
+        int s0 = 0;
+        for (int l = 0; l < n_lanes; ++l) {
+            const int nl = (cfg->n_streams - s0) / (n_lanes - l);
+            vs_tracker_config lc = *cfg;
+            lc.n_streams = nl;
+            lc.pipeline_lanes = 1;
+            lc.capacity = cap;
+            vs_tracker* lane = nullptr;
+            const int rc = vs_tracker_create(&lc, nullptr, &lane);
+            if (rc != VS_OK) { vs_tracker_destroy(t); return rc; }
+            if (cudaEventCreateWithFlags(&lane->ev_done, cudaEventDisableTiming) != cudaSuccess) {
+                vs_tracker_destroy(lane); vs_tracker_destroy(t); set_error("lane event"); return VS_ERR_CUDA;
+            }
+            t->lanes.push_back(lane);
+            t->lane_s0.push_back(s0);
+            s0 += nl;
+        }
+        t->lane_s0.push_back(s0);
+        if (effective) *effective = t->cfg;
+        *out = t;
+        return VS_OK;
+    }
+    t->cfg.pipeline_lanes = 1;
     t->n_bound = cfg->max_cnt;
     plan_pyramid(t);
     t->raw_pitch = round_up(t->W, 16);
@@ -414,6 +449,9 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
 void vs_tracker_destroy(vs_tracker* t) {
     if (!t) return;
     cudaSetDevice(t->cfg.device);
+    for (vs_tracker* lane : t->lanes) vs_tracker_destroy(lane);
+    t->lanes.clear();
+    if (t->ev_done) cudaEventDestroy(t->ev_done);
     if (t->stream) cudaStreamSynchronize(t->stream);
     t->arena.release();
     if (t->d_eig) cudaFree(t->d_eig);
@@ -621,22 +659,38 @@ static void fill_results(vs_tracker* t, vs_track_result* out) {
 
 }  // namespace vs
 
-extern "C" {
+namespace vs {
 
-int vs_tracker_fetch_results(vs_tracker* t, vs_track_result* out) {
-    if (!t || !out) { set_error("null argument"); return VS_ERR_INVALID; }
-    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
-    VS_CUDA_TRY(cudaMemcpyAsync(t->h_block, t->d_rblock, t->h_block_bytes, cudaMemcpyDeviceToHost, t->stream));
-    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
-    fill_results(t, out);
+// ---- asynchronous halves of a frame call (everything is enqueued on t->stream; nothing waits) ----
+
+// host frames -> d_raw.  Tightly packed frames go up as 1-D copies, and runs of frames that are also
+// consecutive in host memory as ONE copy (a 2-D copy per frame costs a driver call each and, for widths
+// that are not a multiple of 64, an order of magnitude in PCIe efficiency).
+static int enqueue_upload(vs_tracker* t, const uint8_t* const* frames, int stride) {
+    const int64_t img_bytes = (int64_t)t->W * t->H;
+    const bool packed = stride == t->W && t->raw_pitch == t->W && t->raw_stride == img_bytes;
+    for (int s = 0; s < t->B; ++s)
+        if (!frames[s]) { set_error("frames[%d] is null", s); return VS_ERR_INVALID; }
+    if (packed) {
+        int s = 0;
+        while (s < t->B) {
+            int e = s + 1;
+            while (e < t->B && frames[e] == frames[e - 1] + img_bytes) ++e;
+            VS_CUDA_TRY(cudaMemcpyAsync(t->d_raw + (int64_t)s * t->raw_stride, frames[s], (size_t)(img_bytes * (e - s)),
+                                        cudaMemcpyHostToDevice, t->stream));
+            s = e;
+        }
+    } else {
+        for (int s = 0; s < t->B; ++s)
+            VS_CUDA_TRY(cudaMemcpy2DAsync(t->d_raw + (int64_t)s * t->raw_stride, t->raw_pitch, frames[s], stride, t->W,
+                                          t->H, cudaMemcpyHostToDevice, t->stream));
+    }
     return VS_OK;
 }
 
-int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_t stride, int64_t image_stride_bytes,
-                                  const double* time_s, int32_t results_to_host, vs_track_result* out) {
-    if (!t || !d_frames || !time_s) { set_error("null argument"); return VS_ERR_INVALID; }
-    if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
-    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+// one frame per stream, images resident on the device
+static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride, int64_t image_stride_bytes,
+                         const double* time_s) {
     memcpy(t->h_time, time_s, sizeof(double) * t->B);
     VS_CUDA_TRY(cudaEventRecord(t->ev0, t->stream));
     prof_begin(t);
@@ -657,6 +711,77 @@ int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_
     if (rc != VS_OK) return rc;
     VS_CUDA_TRY(cudaEventRecord(t->ev1, t->stream));
     prof_end(t);
+    return VS_OK;
+}
+
+static int enqueue_fetch(vs_tracker* t) {
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_block, t->d_rblock, t->h_block_bytes, cudaMemcpyDeviceToHost, t->stream));
+    return VS_OK;
+}
+
+// lanes: make every lane's stream wait for work already queued on the parent stream (fork) ...
+static int lanes_fork(vs_tracker* t) {
+    VS_CUDA_TRY(cudaEventRecord(t->ev0, t->stream));
+    for (vs_tracker* lane : t->lanes) VS_CUDA_TRY(cudaStreamWaitEvent(lane->stream, t->ev0, 0));
+    return VS_OK;
+}
+// ... and the parent stream wait for every lane (join), so events recorded on the parent stream bracket the call
+static int lanes_join(vs_tracker* t) {
+    for (vs_tracker* lane : t->lanes) {
+        VS_CUDA_TRY(cudaEventRecord(lane->ev_done, lane->stream));
+        VS_CUDA_TRY(cudaStreamWaitEvent(t->stream, lane->ev_done, 0));
+    }
+    VS_CUDA_TRY(cudaEventRecord(t->ev1, t->stream));
+    return VS_OK;
+}
+
+}  // namespace vs
+
+extern "C" {
+
+int vs_tracker_fetch_results(vs_tracker* t, vs_track_result* out) {
+    if (!t || !out) { set_error("null argument"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    if (!t->lanes.empty()) {
+        for (vs_tracker* lane : t->lanes) { const int rc = enqueue_fetch(lane); if (rc != VS_OK) return rc; }
+        for (size_t l = 0; l < t->lanes.size(); ++l) {
+            VS_CUDA_TRY(cudaStreamSynchronize(t->lanes[l]->stream));
+            fill_results(t->lanes[l], out + t->lane_s0[l]);
+        }
+        return VS_OK;
+    }
+    const int rc = enqueue_fetch(t);
+    if (rc != VS_OK) return rc;
+    VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+    fill_results(t, out);
+    return VS_OK;
+}
+
+int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_t stride, int64_t image_stride_bytes,
+                                  const double* time_s, int32_t results_to_host, vs_track_result* out) {
+    if (!t || !d_frames || !time_s) { set_error("null argument"); return VS_ERR_INVALID; }
+    if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    if (!t->lanes.empty()) {
+        int rc = lanes_fork(t);
+        if (rc != VS_OK) return rc;
+        for (size_t l = 0; l < t->lanes.size(); ++l) {
+            const int s0 = t->lane_s0[l];
+            rc = enqueue_frame(t->lanes[l], d_frames + (int64_t)s0 * image_stride_bytes, stride, image_stride_bytes, time_s + s0);
+            if (rc != VS_OK) return rc;
+        }
+        rc = lanes_join(t);
+        if (rc != VS_OK) return rc;
+        if (results_to_host && out) {
+            rc = vs_tracker_fetch_results(t, out);
+            if (rc != VS_OK) return rc;
+            VS_CUDA_TRY(cudaEventSynchronize(t->ev1));
+            cudaEventElapsedTime(&t->last_ms, t->ev0, t->ev1);
+        }
+        return VS_OK;
+    }
+    const int rc = enqueue_frame(t, d_frames, stride, image_stride_bytes, time_s);
+    if (rc != VS_OK) return rc;
     if (results_to_host && out) {
         const int rc2 = vs_tracker_fetch_results(t, out);
         if (rc2 != VS_OK) return rc2;
@@ -670,11 +795,31 @@ int vs_tracker_track_batch(vs_tracker* t, const uint8_t* const* frames, int32_t 
     if (!t || !frames || !time_s || !out) { set_error("null argument"); return VS_ERR_INVALID; }
     if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
     VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
-    for (int s = 0; s < t->B; ++s) {
-        if (!frames[s]) { set_error("frames[%d] is null", s); return VS_ERR_INVALID; }
-        VS_CUDA_TRY(cudaMemcpy2DAsync(t->d_raw + (int64_t)s * t->raw_stride, t->raw_pitch, frames[s], stride, t->W, t->H,
-                                      cudaMemcpyHostToDevice, t->stream));
+    if (!t->lanes.empty()) {
+        // lane l: upload -> kernels -> result download on its own stream; the copy engines work on lane l+1
+        // while the SMs run lane l
+        int rc = lanes_fork(t);
+        if (rc != VS_OK) return rc;
+        for (size_t l = 0; l < t->lanes.size(); ++l) {
+            vs_tracker* lane = t->lanes[l];
+            const int s0 = t->lane_s0[l];
+            rc = enqueue_upload(lane, frames + s0, stride);
+            if (rc == VS_OK) rc = enqueue_frame(lane, lane->d_raw, lane->raw_pitch, lane->raw_stride, time_s + s0);
+            if (rc == VS_OK) rc = enqueue_fetch(lane);
+            if (rc != VS_OK) return rc;
+        }
+        rc = lanes_join(t);
+        if (rc != VS_OK) return rc;
+        for (size_t l = 0; l < t->lanes.size(); ++l) {
+            VS_CUDA_TRY(cudaStreamSynchronize(t->lanes[l]->stream));
+            fill_results(t->lanes[l], out + t->lane_s0[l]);
+        }
+        VS_CUDA_TRY(cudaEventSynchronize(t->ev1));
+        cudaEventElapsedTime(&t->last_ms, t->ev0, t->ev1);
+        return VS_OK;
     }
+    int rc = enqueue_upload(t, frames, stride);
+    if (rc != VS_OK) return rc;
     return vs_tracker_track_batch_device(t, t->d_raw, t->raw_pitch, t->raw_stride, time_s, 1, out);
 }
 
@@ -688,6 +833,11 @@ int vs_tracker_track(vs_tracker* t, const uint8_t* gray, int32_t stride, double 
 int vs_tracker_set_params(vs_tracker* t, int32_t max_cnt, int32_t min_dist, double f_threshold, int32_t lk_window,
                           int32_t lk_pyramid, int32_t lk_iterations, double lk_eps, double f_edge_factor) {
     if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    for (vs_tracker* lane : t->lanes) {
+        const int rc = vs_tracker_set_params(lane, max_cnt, min_dist, f_threshold, lk_window, lk_pyramid, lk_iterations,
+                                             lk_eps, f_edge_factor);
+        if (rc != VS_OK) return rc;
+    }
     if (max_cnt > 0) {
         if (max_cnt > t->cap) { set_error("max_cnt %d above handle capacity %d", max_cnt, t->cap); return VS_ERR_CAPACITY; }
         t->cfg.max_cnt = max_cnt;
@@ -718,6 +868,17 @@ int vs_tracker_set_reject_callback(vs_tracker* t, vs_reject_fn fn, void* user) {
 int vs_tracker_reset(vs_tracker* t, int32_t stream) {
     if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
     VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    if (!t->lanes.empty()) {
+        if (stream >= t->B) { set_error("bad stream"); return VS_ERR_INVALID; }
+        for (size_t l = 0; l < t->lanes.size(); ++l) {
+            const int s0 = t->lane_s0[l], s1 = t->lane_s0[l + 1];
+            if (stream < 0 || (stream >= s0 && stream < s1)) {
+                const int rc = vs_tracker_reset(t->lanes[l], stream < 0 ? -1 : stream - s0);
+                if (rc != VS_OK) return rc;
+            }
+        }
+        return VS_OK;
+    }
     if (stream < 0) {
         VS_CUDA_TRY(cudaMemsetAsync(t->g.n, 0, sizeof(int) * t->B, t->stream));
         t->has_prev = false;
@@ -729,11 +890,17 @@ int vs_tracker_reset(vs_tracker* t, int32_t stream) {
     return VS_OK;
 }
 
-int64_t vs_tracker_launch_count(const vs_tracker* t) { return t ? t->launches : 0; }
+int64_t vs_tracker_launch_count(const vs_tracker* t) {
+    if (!t) return 0;
+    int64_t n = t->launches;
+    for (const vs_tracker* lane : t->lanes) n += lane->launches;
+    return n;
+}
 void* vs_tracker_cuda_stream(const vs_tracker* t) { return t ? (void*)t->stream : nullptr; }
 
 int vs_tracker_set_profiling(vs_tracker* t, int32_t on) {
     if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    for (vs_tracker* lane : t->lanes) vs_tracker_set_profiling(lane, on);
     t->prof.on = on != 0;
     if (on)
         for (int i = 0; i < PK_COUNT; ++i) { t->prof.total_ms[i] = 0.0; t->prof.launches[i] = 0; }
@@ -744,6 +911,8 @@ int vs_tracker_get_profile(const vs_tracker* t, int32_t max_n, float* total_ms, 
     if (!t || !total_ms || !launches || !n_out) { set_error("null argument"); return VS_ERR_INVALID; }
     const int n = max_n < PK_COUNT ? max_n : (int)PK_COUNT;
     for (int i = 0; i < n; ++i) { total_ms[i] = (float)t->prof.total_ms[i]; launches[i] = t->prof.launches[i]; }
+    for (const vs_tracker* lane : t->lanes)
+        for (int i = 0; i < n; ++i) { total_ms[i] += (float)lane->prof.total_ms[i]; launches[i] += lane->prof.launches[i]; }
     *n_out = n;
     return VS_OK;
 }
@@ -759,8 +928,9 @@ float vs_tracker_last_device_ms(const vs_tracker* t) { return t ? t->last_ms : 0
 // =================================================================================================
 namespace vs {
 
-static int stage_begin(vs_tracker* t) {
+static int stage_begin(vs_tracker*& t) {
     if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    if (!t->lanes.empty()) t = t->lanes[0];      // stage entry points use one stream slot: lane 0 is a full handle
     VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
     sync_glue_params(t);
     return upload_disc(t);

@@ -85,5 +85,10 @@ struct vs_tracker {
     std::vector<int> disc_hw_host;
     int disc_radius = -1;
     vs::Profiler prof;
+    // pipeline lanes (cfg.pipeline_lanes > 1): this handle then owns no device buffers of its own, only `stream`
+    // (fork/join point) and the lanes; lane l tracks streams [lane_s0[l], lane_s0[l+1])
+    std::vector<vs_tracker*> lanes;
+    std::vector<int> lane_s0;
+    cudaEvent_t ev_done = nullptr;    // recorded on `stream` after the lane's last kernel (join)
 };
 

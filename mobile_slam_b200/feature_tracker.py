@@ -41,6 +41,7 @@ class TrackerConfig:
     capacity: int = 0
     device: int = 0
     first_feature_id: int = 0
+    pipeline_lanes: int = 0
     fisheye_mask: np.ndarray | None = None
 
 
@@ -86,6 +87,7 @@ def _fill_config(tc: TrackerConfig, cam: CameraParams, n_streams: int):
     c.lk_iterations, c.lk_eps = tc.lk_iterations, tc.lk_eps
     c.fb_check, c.fb_threshold = tc.fb_check, tc.fb_threshold
     c.ransac_mode, c.capacity, c.first_feature_id = tc.ransac_mode, tc.capacity, tc.first_feature_id
+    c.pipeline_lanes = tc.pipeline_lanes
     keep = None
     if tc.fisheye_mask is not None:
         keep = np.ascontiguousarray(tc.fisheye_mask, np.uint8)

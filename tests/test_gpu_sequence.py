@@ -132,3 +132,30 @@ def test_param_mutators_and_errors(built_lib):
     with pytest.raises(ValueError):
         bt.track([np.zeros((10, 10), np.uint8)], [0.1])
     bt.close()
+
+
+def test_pipeline_lanes_match_single_lane(built_lib):
+    # a handle split into pipeline lanes (own CUDA stream each, H2D overlapped with kernels) must return exactly what
+    # the single-lane handle returns, stream by stream
+    cfg = CONFIGS["C1"]
+    S = 6
+    streams = [SynthStream(300 + s, cfg["width"], cfg["height"]) for s in range(S)]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    one = BatchTracker(tc, cam, S)
+    tc4, _ = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, pipeline_lanes=4)
+    many = BatchTracker(tc4, cam, S)
+    for k in range(6):
+        frames = np.stack([st.frame(k) for st in streams])            # contiguous block -> coalesced upload path
+        a = one.track([f for f in frames], [0.05 * k] * S)
+        b = many.track([frames[s] for s in range(S)], [0.05 * k] * S)
+        for s in range(S):
+            assert a[s].ids.tolist() == b[s].ids.tolist() and a[s].track_cnt.tolist() == b[s].track_cnt.tolist()
+            assert np.array_equal(a[s].cur_pts, b[s].cur_pts)
+            assert np.array_equal(a[s].pts_velocity, b[s].pts_velocity)
+    assert many.launch_count > 0 and many.last_device_ms > 0
+    many.reset(2)
+    many.set_params(max_cnt=100)
+    r = many.track([st.frame(6) for st in streams], [0.3] * S)
+    assert len(r) == S and all(len(x.ids) > 0 for x in r[:2])
+    one.close()
+    many.close()

@@ -93,6 +93,7 @@ class ClockSampler:
 
     def __init__(self, gpu_index: int):
         self.rows = []
+        self.all_rows = []       # every sample since start(): fallback when a timed region is shorter than one period
         self.proc = None
         self.gpu = gpu_index
         self.active = False
@@ -101,7 +102,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                  "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -111,6 +112,7 @@ class ClockSampler:
     def _pump(self):
         for line in self.proc.stdout:
             with self._lock:
+                self.all_rows.append(line.strip())
                 if self.active:
                     self.rows.append(line.strip())
 
@@ -130,7 +132,7 @@ class ClockSampler:
         sm, mx, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         with self._lock:
-            rows = list(self.rows)
+            rows = list(self.rows) if len(self.rows) >= 2 else list(self.all_rows[-50:])
         for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 9:

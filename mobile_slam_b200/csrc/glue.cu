@@ -117,7 +117,11 @@ static __host__ __device__ inline int pow2_at_least(int n) {
     return p;
 }
 constexpr int kFixedPointMax = 768;   // above this the greedy keep runs warp-serial
-int set_mask_smem_bytes(int cap) { return pow2_at_least(cap) * 8 + cap * (4 + 4 + 4 + 4 + 4 + 4 + 4); }
+int set_mask_smem_bytes(int cap) {
+    const int words = (cap + 31) / 32;
+    const int conf = cap <= kFixedPointMax ? cap * words * 4 : 0;      // conflict bit matrix of the fixed-point greedy
+    return pow2_at_least(cap) * 8 + cap * (4 + 4 + 4 + 4 + 4 + 4 + 4) + conf + 3 * words * 4 + 16;
+}
 
 __device__ __forceinline__ void bitonic_sort_desc_u64(unsigned long long* v, int N, int tid, int nthreads) {
     for (int k = 2; k <= N; k <<= 1) {
@@ -180,58 +184,89 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
         for (int i = tid; i < n2; i += 256) perm[i] = (int)(ck[i] & 0xFFFFull);
     }
     __syncthreads();
-    if (n2 <= kFixedPointMax) {
+    if (n2 <= kFixedPointMax && g.cap <= kFixedPointMax) {
         // Greedy keep (feature_tracker.cpp:79-86) as a fixed point: kept[q] = base(q) && no kept a < q whose
         // disc covers q.  The recurrence is triangular, so Jacobi sweeps from "all base-ok points kept"
         // reach its unique solution — the sequential result — after (longest rejection chain + 1) sweeps.
+        // The pair tests are hoisted out of the sweeps into a conflict bit matrix (row q, bit a: a < q and
+        // the disc of a covers q) built with all threads in parallel; a sweep is then nw ANDs per point.
         const int R = g.min_dist;
-        int* cur = lpos;
-        int* nxt = rpos;
-        for (int q = tid; q < n2; q += 256) {
-            const float2 p = g.w_next[o + src[perm[q]]];
-            const int rx = cv_round(p.x), ry = cv_round(p.y);
-            acc[q] = make_short2((short)rx, (short)ry);
-            cur[q] = g.base_mask[(int64_t)ry * g.mask_pitch + rx] == 255;
-            kidx[q] = cur[q];                        // base-ok flag, fixed
+        const int nw = (n2 + 31) >> 5;
+        uint32_t* conf = reinterpret_cast<uint32_t*>(acc + g.cap);      // [n2][nw]
+        uint32_t* kb0 = conf + (size_t)g.cap * ((g.cap + 31) >> 5);     // kept bit masks, double buffered
+        uint32_t* kb1 = kb0 + ((g.cap + 31) >> 5);
+        uint32_t* baseb = kb1 + ((g.cap + 31) >> 5);
+        for (int q0 = 0; q0 < n2; q0 += 256) {
+            const int q = q0 + tid;
+            bool b = false;
+            if (q < n2) {
+                const float2 p = g.w_next[o + src[perm[q]]];
+                const int rx = cv_round(p.x), ry = cv_round(p.y);
+                acc[q] = make_short2((short)rx, (short)ry);
+                b = g.base_mask[(int64_t)ry * g.mask_pitch + rx] == 255;
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, b);
+            if (lane == 0 && q0 + (tid & ~31) < n2) {
+                baseb[(q0 + tid) >> 5] = bal;
+                kb0[(q0 + tid) >> 5] = bal;
+            }
         }
         __syncthreads();
+        for (int idx = tid; idx < n2 * nw; idx += 256) {
+            const int q = idx / nw, w = idx - q * nw;
+            uint32_t bits = 0;
+            const int a0 = 32 * w;
+            if (a0 < q) {
+                const int rx = acc[q].x, ry = acc[q].y;
+                const int na = min(32, q - a0);
+                for (int b = 0; b < na; ++b) {
+                    const short2 c = acc[a0 + b];
+                    const int dy = abs(ry - (int)c.y), dx = abs(rx - (int)c.x);
+                    if (dy <= R && dx <= __ldg(g.disc_hw + dy)) bits |= 1u << b;
+                }
+            }
+            conf[idx] = bits;
+        }
+        __syncthreads();
+        uint32_t* cur = kb0;
+        uint32_t* nxt = kb1;
         for (int sweep = 0; sweep <= n2; ++sweep) {
             int changed = 0;
-            for (int q = tid; q < n2; q += 256) {
-                int k = kidx[q];
-                if (k) {
-                    const int rx = acc[q].x, ry = acc[q].y;
-                    for (int a = 0; a < q; ++a) {
-                        if (!cur[a]) continue;
-                        const int dy = abs(ry - (int)acc[a].y), dx = abs(rx - (int)acc[a].x);
-                        if (dy <= R && dx <= g.disc_hw[dy]) {
-                            k = 0;
-                            break;
-                        }
-                    }
+            for (int q0 = 0; q0 < n2; q0 += 256) {
+                const int q = q0 + tid;
+                bool k = false;
+                if (q < n2) {
+                    k = (baseb[q >> 5] >> (q & 31)) & 1u;
+                    const uint32_t* row = conf + q * nw;
+                    for (int w = 0; k && w <= (q >> 5); ++w)
+                        if (row[w] & cur[w]) k = false;
                 }
-                nxt[q] = k;
-                changed |= (k != cur[q]);
+                const unsigned bal = __ballot_sync(0xffffffffu, k);
+                if (lane == 0 && q0 + (tid & ~31) < n2) {
+                    const int wi = (q0 + tid) >> 5;
+                    nxt[wi] = bal;
+                    changed |= (bal != cur[wi]);
+                }
             }
             const int any = __syncthreads_or(changed);
-            int* t = cur;
+            uint32_t* t = cur;
             cur = nxt;
             nxt = t;
             if (!any) break;
         }
-        // ordered compaction of the kept points
-        int base = 0;
-        for (int chunk = 0; chunk < n2; chunk += 256) {
-            const int q = chunk + tid;
-            const bool ok = q < n2 && cur[q];
-            const int widx = q < n2 ? src[perm[q]] : 0;
-            __syncthreads();                         // kidx is about to be reused as the kept list
-            const int slot = block_compact_slot(ok, tid, s_warp_cnt, base);
-            if (slot >= 0) nxt[slot] = widx;
+        // ordered compaction of the kept points straight from the bit mask
+        for (int q = tid; q < n2; q += 256) {
+            if ((cur[q >> 5] >> (q & 31)) & 1u) {
+                int slot = __popc(cur[q >> 5] & ((1u << (q & 31)) - 1u));
+                for (int w = 0; w < (q >> 5); ++w) slot += __popc(cur[w]);
+                kidx[slot] = src[perm[q]];
+            }
         }
-        __syncthreads();
-        for (int j = tid; j < base; j += 256) kidx[j] = nxt[j];
-        if (tid == 0) s_kn = base;
+        if (tid == 0) {
+            int tot = 0;
+            for (int w = 0; w < nw; ++w) tot += __popc(cur[w]);
+            s_kn = tot;
+        }
     } else if (tid < 32) {
         const int R = g.min_dist;
         int A = 0;

@@ -37,6 +37,8 @@ struct LkParams {
     int cap;
     float2* next_pts;         // [n_streams][cap]
     uint8_t* status;          // [n_streams][cap] raw LK status
+    int* work_counters;       // [2] persistent-warp work queue heads (zeroed at create), alternated by work_seq
+    int work_seq;             // launch sequence number of this handle
 };
 int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches);
 

@@ -303,15 +303,9 @@ __device__ __forceinline__ void load_aligned3(const uint32_t* trow, int sb, uint
     a2 = w2 >> sh;
 }
 
-__global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_fast21_kernel(LkParams p) {
+// one feature (stream s, slot i) on one warp
+__device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int i, uint32_t* tile, int lane) {
     constexpr int WIN = 21, NSEG = 3, NRUN = WIN * NSEG;
-    __shared__ __align__(16) uint32_t s_tiles[kLkWarpsPerCta][kFastWarpSmem / 4];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int s = blockIdx.y;
-    const int i = blockIdx.x * kLkWarpsPerCta + warp;
-    const int n = p.counts[s];
-    if (i >= n) return;
-    uint32_t* tile = s_tiles[warp];
     const float hw = (float)(WIN - 1) * 0.5f;
 
     // this lane's two runs: run r -> window row r / 3, first window column 7 * (r % 3)
@@ -508,12 +502,45 @@ __global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_fast21_kernel(LkParams
     }
 }
 
+// Persistent warps: features finish after very different iteration counts (1 .. 30 per level), so a fixed
+// feature -> warp map leaves CTAs waiting for their slowest warp.  Every warp instead pulls the next
+// (stream, slot) work item from a global counter until the batch is drained.  Two counters alternate between
+// launches: launch k drains counter k&1 and clears the other one for launch k+1 (stream order makes that safe).
+__global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_fast21_kernel(LkParams p, int n_streams, int max_features,
+                                                                        int* counters, int which) {
+    __shared__ __align__(16) uint32_t s_tiles[kLkWarpsPerCta][kFastWarpSmem / 4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (blockIdx.x == 0 && threadIdx.x == 0) counters[which ^ 1] = 0;
+    uint32_t* tile = s_tiles[warp];
+    const int total = n_streams * max_features;
+    int* ctr = counters + which;
+    for (;;) {
+        int w = 0;
+        if (lane == 0) w = atomicAdd(ctr, 1);
+        w = __shfl_sync(0xffffffffu, w, 0);
+        if (w >= total) break;
+        const int s = w / max_features, i = w - s * max_features;
+        if (i < __ldg(p.counts + s)) lk_fast21_feature(p, s, i, tile, lane);
+        __syncwarp();
+    }
+}
+
 int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches) {
     if (p.win < 3 || p.win > kMaxWin || (p.win & 1) == 0) return -1;
     if (max_features <= 0 || p.n_levels <= 0) return 0;
     dim3 grid((max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta, n_streams);
-    if (p.win == 21) {
-        lk_fast21_kernel<<<grid, 32 * kLkWarpsPerCta, 0, st>>>(p);
+    if (p.win == 21 && p.work_counters) {
+        static int resident = 0;
+        if (!resident) {
+            int dev = 0, sms = 148, per_sm = 2;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lk_fast21_kernel, 32 * kLkWarpsPerCta, 0);
+            resident = sms * (per_sm > 0 ? per_sm : 1);
+        }
+        const int need = (n_streams * max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta;
+        lk_fast21_kernel<<<need < resident ? need : resident, 32 * kLkWarpsPerCta, 0, st>>>(p, n_streams, max_features,
+                                                                                          p.work_counters, p.work_seq & 1);
     } else {
         const int smem = kLkWarpsPerCta * lk_warp_smem(p.win);
         static bool attr_set = false;

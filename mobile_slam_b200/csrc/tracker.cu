@@ -337,6 +337,7 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     VS_TRY_CREATE(A.alloc(&t->d_disc_hw, (size_t)kMaxDiscRadius + 1));
     VS_TRY_CREATE(A.alloc(&t->d_fish_hw, (size_t)(t->W > t->H ? t->W : t->H) + 2));
     VS_TRY_CREATE(A.alloc(&t->d_cur_time, (size_t)B));
+    VS_TRY_CREATE(A.alloc(&t->d_lk_counters, (size_t)2));
     g.cur_time = t->d_cur_time;
     VS_TRY_CREATE(A.alloc(&g.n, B));
     VS_TRY_CREATE(A.alloc(&g.pts, B * C));
@@ -500,6 +501,8 @@ static void fill_lk_params(vs_tracker* t, LkParams& p, int prev_buf, int next_bu
     p.cap = t->cap;
     p.next_pts = out;
     p.status = status;
+    p.work_counters = t->d_lk_counters;
+    p.work_seq = t->lk_seq++;
 }
 
 // build the pyramid of the new frame into buffer `buf` from a device image

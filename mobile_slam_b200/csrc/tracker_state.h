@@ -66,6 +66,8 @@ struct vs_tracker {
     int* d_fish_hw = nullptr;     // row half widths of the auto fisheye circle
     int base_mode = 0, fcx = 0, fcy = 0, fr = 0;   // StParams::base_mode and the circle
     double* d_cur_time = nullptr;
+    int* d_lk_counters = nullptr; // persistent-warp LK work queue heads
+    int lk_seq = 0;
     float* d_eig = nullptr;       // lazily allocated dense eig map (stage API only)
     vs::GlueParams g{};
     // pinned host mirrors

@@ -159,3 +159,29 @@ def test_pipeline_lanes_match_single_lane(built_lib):
     assert len(r) == S and all(len(x.ids) > 0 for x in r[:2])
     one.close()
     many.close()
+
+
+def test_sequence_device_ransac_statistical_parity(built_lib):
+    # VS_RANSAC_DEVICE vs the reference with cv::findFundamentalMat: free-running sequences diverge slowly once the
+    # two RANSACs disagree on a borderline point (SURVEY.md §7 hard part 4), so compare statistics, not ids
+    from mobile_slam_b200 import VS_RANSAC_DEVICE
+    cfg = CONFIGS["C2"]
+    st = SynthStream(31, cfg["width"], cfg["height"], motion=2.0)
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_DEVICE)
+    bt = BatchTracker(tc, cam, 1)
+    ref = R.RefFeatureTracker(R.config_from_synth(cfg, use_ransac=True), ocam.from_config(cfg))
+    pub_g, pub_r, ran, rej = [], [], 0, []
+    for k in range(40):
+        f = st.frame(k)
+        r = bt.track([f], [0.05 * k])[0]
+        ref.detect_and_track(f, 0.05 * k)
+        ref.update_all_ids()
+        pub_g.append(int(np.sum(r.track_cnt > 1)))
+        pub_r.append(sum(1 for c in ref.track_cnt if c > 1))
+        ran += r.counters["ransac_ran"]
+        if r.counters["ransac_ran"]:
+            rej.append(1.0 - r.counters["n_ransac_out"] / max(r.counters["n_ransac_in"], 1))
+    assert ran >= 20, f"RANSAC gate fired on only {ran} frames"
+    assert np.mean(rej) < 0.10, f"device RANSAC rejects {np.mean(rej):.3f} of the tracked points per frame"
+    assert abs(np.mean(pub_g[2:]) - np.mean(pub_r[2:])) <= 0.05 * np.mean(pub_r[2:]), (np.mean(pub_g), np.mean(pub_r))
+    bt.close()

@@ -20,12 +20,12 @@ namespace vs {
 // picks the CTA size from the tile area), so the byte counters cannot overflow.  The private
 // counters are then summed with packed 16-bit adds.
 // ---------------------------------------------------------------------------------------------
-template <int NT>
+template <int NT, bool FULLW>
 __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict__ src, int pitch, int64_t img_stride,
                                                        int tw, int th, int clip, float lut_scale,
                                                        uint8_t* __restrict__ luts) {
     extern __shared__ __align__(16) uint32_t s_cnt[];          // [64 word rows][NT threads]
-    __shared__ uint32_t s_part[NT / 64][64][2];
+    __shared__ uint32_t s_part[NT >= 64 ? NT / 64 : 1][64][2];
     __shared__ int s_hist[256];
     __shared__ unsigned int s_warp_tot[NT / 32];
     __shared__ unsigned int s_clipped;
@@ -71,38 +71,61 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const uint32_t b = (v[u] >> (8 * k)) & 255u;
-                const uint32_t inc = (k >= lo[u] && k < hi[u]) ? (1u << ((b >> 3) & 0x18u)) : 0u;
+                // FULLW: every tile starts on a word boundary and is a whole number of words wide, so only the
+                // past-the-end slots of the last trip (lo = 4) are invalid: one test per word instead of two per pixel
+                const uint32_t inc = (FULLW ? lo[u] == 0 : (k >= lo[u] && k < hi[u])) ? (1u << ((b >> 3) & 0x18u)) : 0u;
                 mine[(b & 63u) * NT] += inc;
             }
         }
     }
     __syncthreads();
-    // sum the NT private copies: thread -> (word row r, 64-column group cg), rotated so lanes hit distinct banks
-    {
-        const int r = tid & 63, cg = tid >> 6;
-        uint32_t a = 0, b = 0;      // packed 16-bit sums of bytes (0, 2) and (1, 3)
-        const uint32_t* row = s_cnt + r * NT + cg * 64;
-#pragma unroll 8
-        for (int j = 0; j < 64; ++j) {
-            const uint32_t w = row[(j + lane) & 63];
-            a += w & 0x00FF00FFu;
-            b += (w >> 8) & 0x00FF00FFu;
-        }
-        s_part[cg][r][0] = a;
-        s_part[cg][r][1] = b;
-    }
-    __syncthreads();
-    if (tid < 64) {
-        uint32_t a = 0, b = 0;
+    // sum the NT private copies (packed 16-bit sums of bytes (0, 2) and (1, 3)), rotated so lanes hit distinct banks
+    if constexpr (NT == 32) {
+        // one warp per tile: lane sums word rows lane and lane + 32 over the 32 copies (<= 32 * 255 per 16-bit lane)
 #pragma unroll
-        for (int cg = 0; cg < NT / 64; ++cg) {     // per-16-bit-lane totals stay below 65536 (tile area checked by the launcher)
-            a += s_part[cg][tid][0];
-            b += s_part[cg][tid][1];
+        for (int rr = 0; rr < 2; ++rr) {
+            const int r = tid + 32 * rr;
+            uint32_t a = 0, b = 0;
+            const uint32_t* row = s_cnt + r * NT;
+#pragma unroll 8
+            for (int j = 0; j < 32; ++j) {
+                const uint32_t w = row[(j + lane) & 31];
+                a += w & 0x00FF00FFu;
+                b += (w >> 8) & 0x00FF00FFu;
+            }
+            s_hist[r] = (int)(a & 0xFFFFu);
+            s_hist[r + 64] = (int)(b & 0xFFFFu);
+            s_hist[r + 128] = (int)(a >> 16);
+            s_hist[r + 192] = (int)(b >> 16);
         }
-        s_hist[tid] = (int)(a & 0xFFFFu);            // byte 0 -> bin r
-        s_hist[tid + 64] = (int)(b & 0xFFFFu);       // byte 1 -> bin r + 64
-        s_hist[tid + 128] = (int)(a >> 16);          // byte 2 -> bin r + 128
-        s_hist[tid + 192] = (int)(b >> 16);          // byte 3 -> bin r + 192
+    } else {
+        // thread -> (word row r, 64-column group cg)
+        {
+            const int r = tid & 63, cg = tid >> 6;
+            uint32_t a = 0, b = 0;
+            const uint32_t* row = s_cnt + r * NT + cg * 64;
+#pragma unroll 8
+            for (int j = 0; j < 64; ++j) {
+                const uint32_t w = row[(j + lane) & 63];
+                a += w & 0x00FF00FFu;
+                b += (w >> 8) & 0x00FF00FFu;
+            }
+            s_part[cg][r][0] = a;
+            s_part[cg][r][1] = b;
+        }
+        __syncthreads();
+        if (tid < 64) {
+            uint32_t a = 0, b = 0;
+#pragma unroll
+            for (int cg = 0; cg < NT / 64; ++cg) {     // per-16-bit-lane totals stay below 65536 (tile area checked by the launcher)
+                a += s_part[cg][tid][0];
+                b += s_part[cg][tid][1];
+            }
+            s_hist[tid] = (int)(a & 0xFFFFu);            // byte 0 -> bin r
+            s_hist[tid + 64] = (int)(b & 0xFFFFu);       // byte 1 -> bin r + 64
+            s_hist[tid + 128] = (int)(a >> 16);          // byte 2 -> bin r + 128
+            s_hist[tid + 192] = (int)(b >> 16);          // byte 3 -> bin r + 192
+        }
     }
     __syncthreads();
     // clip, count the excess; thread t owns bins t*BPT .. t*BPT+BPT-1
@@ -365,17 +388,23 @@ static ClaheGeom clahe_geom(int W, int H) {
     return g;
 }
 
-template <int NT>
-static void launch_lut_nt(const uint8_t* src, int src_pitch, int64_t src_stride, const ClaheGeom& g, int n_streams,
-                          uint8_t* luts, cudaStream_t st) {
+template <int NT, bool FULLW>
+static void launch_lut_nt2(const uint8_t* src, int src_pitch, int64_t src_stride, const ClaheGeom& g, int n_streams,
+                           uint8_t* luts, cudaStream_t st) {
     const int smem = 64 * NT * 4;
     static bool configured = false;
     if (!configured && smem > 48 * 1024) {
-        cudaFuncSetAttribute(clahe_lut_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(clahe_lut_kernel<NT, FULLW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = true;
     }
-    clahe_lut_kernel<NT><<<dim3(kClaheTiles * kClaheTiles, n_streams), NT, smem, st>>>(
+    clahe_lut_kernel<NT, FULLW><<<dim3(kClaheTiles * kClaheTiles, n_streams), NT, smem, st>>>(
         src, src_pitch, src_stride, g.tw, g.th, g.clip, g.lut_scale, luts);
+}
+template <int NT>
+static void launch_lut_nt(const uint8_t* src, int src_pitch, int64_t src_stride, const ClaheGeom& g, int n_streams,
+                          uint8_t* luts, cudaStream_t st) {
+    if ((g.tw & 3) == 0) launch_lut_nt2<NT, true>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    else launch_lut_nt2<NT, false>(src, src_pitch, src_stride, g, n_streams, luts, st);
 }
 
 void launch_clahe_lut_only(const uint8_t* src, int src_pitch, int64_t src_stride, int W, int H, int n_streams,
@@ -385,7 +414,9 @@ void launch_clahe_lut_only(const uint8_t* src, int src_pitch, int64_t src_stride
     const bool exact_tiles = (W % kClaheTiles == 0) && (H % kClaheTiles == 0) && (src_pitch % 4 == 0);
     // a thread of the private-counter kernel may see up to 4 * ceil(words/NT) pixels; keep that below 256
     const int words = ((g.tw + 6) / 4 + 1) * g.th;
-    if (exact_tiles && 4 * ((words + 63) / 64) <= 255) launch_lut_nt<64>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    // fewest private copies that fit the byte counters: the merge costs 64 shared-memory reads per copy
+    if (exact_tiles && 4 * ((words + 31) / 32) <= 255) launch_lut_nt<32>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    else if (exact_tiles && 4 * ((words + 63) / 64) <= 255) launch_lut_nt<64>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else if (exact_tiles && 4 * ((words + 127) / 128) <= 255) launch_lut_nt<128>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else if (exact_tiles && 4 * ((words + 255) / 256) <= 255 && area < 65536) launch_lut_nt<256>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else

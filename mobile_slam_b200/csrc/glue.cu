@@ -116,10 +116,13 @@ static __host__ __device__ inline int pow2_at_least(int n) {
     while (p < n) p <<= 1;
     return p;
 }
-constexpr int kFixedPointMax = 768;   // above this the greedy keep runs warp-serial
+constexpr int kFixedPointMax = 768;   // up to here the greedy keep uses a conflict bit matrix, above it neighbour lists
+constexpr int kNbrMax = 12;           // neighbour-list slots per point (overflow -> warp-serial greedy)
+constexpr int kGridCellsMax = 4096;   // cells of the neighbour-search grid
 int set_mask_smem_bytes(int cap) {
     const int words = (cap + 31) / 32;
-    const int conf = cap <= kFixedPointMax ? cap * words * 4 : 0;      // conflict bit matrix of the fixed-point greedy
+    // conflict bit matrix | neighbour lists + search grid (cell starts, fill counters, members)
+    const int conf = cap <= kFixedPointMax ? cap * words * 4 : cap * kNbrMax * 2 + (2 * kGridCellsMax + 1) * 4 + cap * 2;
     return pow2_at_least(cap) * 8 + cap * (4 + 4 + 4 + 4 + 4 + 4 + 4) + conf + 3 * words * 4 + 16;
 }
 
@@ -152,7 +155,8 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
     int* rpos = lpos + g.cap;
     short2* acc = reinterpret_cast<short2*>(rpos + g.cap);   // kept rounded centres
     __shared__ int s_warp_cnt[8];
-    __shared__ int s_kn;
+    __shared__ int s_kn, s_overflow;
+    __shared__ int s_isort[2];
     const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
     const int64_t o = (int64_t)s * g.cap;
     const int wn = g.wn[s];
@@ -171,7 +175,7 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
     __syncthreads();
     // std::sort(track_cnt desc) with libstdc++'s exact tie order: introsort partition phase on one warp,
     // then its final insertion sort == a stable sort of what the partitions left (introsort.cuh)
-    if (tid < 32) warp_introsort_loop_desc(perm, key, n2, lpos, rpos, lane);
+    block_introsort_loop_desc(perm, key, n2, lpos, rpos, kidx, kidx + g.cap / 2, s_isort, tid, 8);
     __syncthreads();
     {
         const int N = pow2_at_least(n2);
@@ -267,7 +271,126 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
             for (int w = 0; w < nw; ++w) tot += __popc(cur[w]);
             s_kn = tot;
         }
-    } else if (tid < 32) {
+    } else {
+        // Large feature sets (cap > kFixedPointMax, e.g. 2000 features): the conflict relation is sparse (kept points
+        // were >= min_dist apart one frame ago), so each point gets a short list of earlier points whose disc covers
+        // it — n^2/2 pair tests spread over the CTA, same-address shared-memory broadcasts — and the greedy is the
+        // same Jacobi fixed point over those lists.  A list overflow falls back to the warp-serial greedy below.
+        const int R = g.min_dist;
+        short* nbr = reinterpret_cast<short*>(acc + g.cap);        // [cap][kNbrMax]
+        int* ncount = key;                                         // track_cnt keys are dead after the sort
+        int* cur = lpos;
+        int* nxt = rpos;
+        if (tid == 0) s_overflow = 0;
+        for (int q = tid; q < n2; q += 256) {
+            const float2 p = g.w_next[o + src[perm[q]]];
+            const int rx = cv_round(p.x), ry = cv_round(p.y);
+            acc[q] = make_short2((short)rx, (short)ry);
+            cur[q] = g.base_mask[(int64_t)ry * g.mask_pitch + rx] == 255;
+            kidx[q] = cur[q];                        // base-ok flag, fixed
+        }
+        __syncthreads();
+        // uniform grid over the rounded centres, cell edge >= R: every disc that can cover a point lies in the 3x3
+        // cells around it, so a point is tested against a handful of earlier points instead of all of them
+        const int cell = R > 16 ? R : 16;
+        const int gx = (g.W + cell - 1) / cell, gy = (g.H + cell - 1) / cell, ncell = gx * gy;
+        int* cstart = reinterpret_cast<int*>(nbr + (size_t)g.cap * kNbrMax);      // [ncell + 1]
+        int* cfill = cstart + kGridCellsMax + 1;                                  // [ncell]
+        short* members = reinterpret_cast<short*>(cfill + kGridCellsMax);         // [cap]
+        const bool use_grid = ncell <= kGridCellsMax;
+        if (use_grid) {
+            for (int c = tid; c <= ncell; c += 256) cstart[c] = 0;
+            for (int c = tid; c < ncell; c += 256) cfill[c] = 0;
+            __syncthreads();
+            for (int q = tid; q < n2; q += 256) {
+                const int cx = min(max((int)acc[q].x, 0) / cell, gx - 1), cy = min(max((int)acc[q].y, 0) / cell, gy - 1);
+                atomicAdd(&cstart[cy * gx + cx + 1], 1);
+            }
+            __syncthreads();
+            if (tid < 32) {                       // exclusive prefix over <= 4096 cells on one warp
+                int carry = 0;
+                for (int c0 = 1; c0 <= ncell; c0 += 32) {
+                    const int c = c0 + lane;
+                    int v = c <= ncell ? cstart[c] : 0;
+#pragma unroll
+                    for (int o2 = 1; o2 < 32; o2 <<= 1) {
+                        const int t = __shfl_up_sync(0xffffffffu, v, o2);
+                        if (lane >= o2) v += t;
+                    }
+                    if (c <= ncell) cstart[c] = v + carry;
+                    carry += __shfl_sync(0xffffffffu, v, 31);
+                }
+            }
+            __syncthreads();
+            for (int q = tid; q < n2; q += 256) {
+                const int cx = min(max((int)acc[q].x, 0) / cell, gx - 1), cy = min(max((int)acc[q].y, 0) / cell, gy - 1);
+                const int c = cy * gx + cx;
+                members[cstart[c] + atomicAdd(&cfill[c], 1)] = (short)q;
+            }
+            __syncthreads();
+        }
+        for (int q = tid; q < n2; q += 256) {
+            const int rx = acc[q].x, ry = acc[q].y;
+            int cnt = 0;
+            auto exact = [&](int a) {
+                const short2 c = acc[a];
+                const int dy = abs(ry - (int)c.y), dx = abs(rx - (int)c.x);
+                if (dy <= R && dx <= __ldg(g.disc_hw + dy)) {
+                    if (cnt < kNbrMax) nbr[q * kNbrMax + cnt] = (short)a;
+                    ++cnt;
+                }
+            };
+            if (use_grid) {
+                const int cx = min(max(rx, 0) / cell, gx - 1), cy = min(max(ry, 0) / cell, gy - 1);
+                for (int yy = max(cy - 1, 0); yy <= min(cy + 1, gy - 1); ++yy) {
+                    const int c0 = yy * gx + max(cx - 1, 0), c1 = yy * gx + min(cx + 1, gx - 1);
+                    for (int j = cstart[c0]; j < cstart[c1 + 1]; ++j) {      // the row's 2-3 cells are contiguous
+                        const int a = members[j];
+                        if (a < q) exact(a);
+                    }
+                }
+            } else {
+                for (int a = 0; a < q; ++a) exact(a);
+            }
+            ncount[q] = cnt;
+            if (cnt > kNbrMax) s_overflow = 1;
+        }
+        __syncthreads();
+        if (!s_overflow) {
+            for (int sweep = 0; sweep <= n2; ++sweep) {
+                int changed = 0;
+                for (int q = tid; q < n2; q += 256) {
+                    int k = kidx[q];
+                    if (k) {
+                        const int c = ncount[q];
+                        for (int j = 0; j < c; ++j)
+                            if (cur[nbr[q * kNbrMax + j]]) { k = 0; break; }
+                    }
+                    nxt[q] = k;
+                    changed |= (k != cur[q]);
+                }
+                const int any = __syncthreads_or(changed);
+                int* t = cur;
+                cur = nxt;
+                nxt = t;
+                if (!any) break;
+            }
+            int base = 0;
+            for (int chunk = 0; chunk < n2; chunk += 256) {
+                const int q = chunk + tid;
+                const bool ok = q < n2 && cur[q];
+                const int widx = q < n2 ? src[perm[q]] : 0;
+                __syncthreads();                     // kidx is about to be reused as the kept list
+                const int slot = block_compact_slot(ok, tid, s_warp_cnt, base);
+                if (slot >= 0) nxt[slot] = widx;
+            }
+            __syncthreads();
+            for (int j = tid; j < base; j += 256) kidx[j] = nxt[j];
+            if (tid == 0) s_kn = base;
+        }
+    }
+    __syncthreads();
+    if (!(n2 <= kFixedPointMax && g.cap <= kFixedPointMax) && s_overflow && tid < 32) {
         const int R = g.min_dist;
         int A = 0;
         for (int q0 = 0; q0 < n2; q0 += 32) {

@@ -182,76 +182,108 @@ __host__ __device__ inline void std_sort_indices(int* v, int n, Comp comp) {
 // left behind; the caller does that with a parallel sort on (key, position).
 // Call with all 32 lanes of one warp; v / key / lpos / rpos live in shared memory.
 // ---------------------------------------------------------------------------------------------
-__device__ inline void warp_introsort_loop_desc(int* v, const int* key, int n, int* lpos, int* rpos, int lane) {
+// one __unguarded_partition_pivot step of [first, last) on a warp; returns the cut.  lpos / rpos: scratch of at least
+// (last - first) ints each, private to this call.
+__device__ inline int warp_partition_desc(int* v, const int* key, int first, int last, int* lpos, int* rpos, int lane) {
     const unsigned full = 0xffffffffu;
-    if (n <= 16) return;
+    DescByKey comp{key};
+    const int mid = first + (last - first) / 2;
+    if (lane == 0) iso_move_median_to_first(v, first, first + 1, mid, last - 1, comp);
+    __syncwarp();
+    const int pk = key[v[first]];
+    const int lo = first + 1;
+    // left stops: key <= pivot key, ascending positions
+    int nL = 0;
+    for (int i0 = lo; i0 < last; i0 += 32) {
+        const int i = i0 + lane;
+        const bool a = i < last && key[v[i]] <= pk;
+        const unsigned bal = __ballot_sync(full, a);
+        if (a) lpos[nL + __popc(bal & ((1u << lane) - 1u))] = i;
+        nL += __popc(bal);
+    }
+    // right stops: key >= pivot key, descending positions
+    int nR = 0;
+    for (int i0 = last - 1; i0 >= lo; i0 -= 32) {
+        const int i = i0 - lane;
+        const bool b = i >= lo && key[v[i]] >= pk;
+        const unsigned bal = __ballot_sync(full, b);
+        if (b) rpos[nR + __popc(bal & ((1u << lane) - 1u))] = i;
+        nR += __popc(bal);
+    }
+    __syncwarp();
+    const int nmin = nL < nR ? nL : nR;
+    int K = nmin;
+    for (int k0 = 0; k0 < nmin; k0 += 32) {
+        const int k = k0 + lane;
+        const bool cross = k < nmin && lpos[k] >= rpos[k];
+        const unsigned bal = __ballot_sync(full, cross);
+        if (bal) {
+            K = k0 + __ffs(bal) - 1;
+            break;
+        }
+    }
+    int cut = last;
+    if (K < nL) cut = lpos[K];
+    if (K >= 1 && rpos[K - 1] < cut) cut = rpos[K - 1];
+    for (int k = lane; k < K; k += 32) {
+        const int a = lpos[k], b = rpos[k];
+        const int t = v[a];
+        v[a] = v[b];
+        v[b] = t;
+    }
+    __syncwarp();
+    return cut;
+}
+
+// __introsort_loop on the whole CTA (blockDim.x = 32 * nwarps): the ranges of one recursion level are disjoint, so
+// the warps partition them concurrently, level by level (the element moves inside a range do not depend on when
+// the range is processed, so the result equals the serial recursion).  queue_a / queue_b: scratch of n / 8 + 2 ints
+// each; lpos / rpos: scratch of n ints each (a range uses its own [first, last) slice).  Must be called by all
+// threads; v / key / scratch live in shared memory.
+__device__ inline void block_introsort_loop_desc(int* v, const int* key, int n, int* lpos, int* rpos, int* queue_a,
+                                                 int* queue_b, int* s_counts /* [2] shared */, int tid, int nwarps) {
+    if (n <= 16) return;                      // uniform
+    const int lane = tid & 31, warp = tid >> 5;
     int lg = 0;
     for (int t = n; t > 1; t >>= 1) ++lg;
-    // explicit stack in registers of lane-uniform values (depth <= 2*lg <= 64 entries is never reached:
-    // every push is matched by shrinking the current range, so 64 slots suffice as in the serial version)
-    int stack_first[64], stack_last[64], stack_depth[64];
-    int sp = 1;
-    stack_first[0] = 0; stack_last[0] = n; stack_depth[0] = 2 * lg;
+    // entry = first | last << 12 | depth << 25   (first < 4096, last <= 4096, depth <= 24)
+    if (tid == 0) {
+        queue_a[0] = 0 | (n << 12) | ((2 * lg) << 25);
+        s_counts[0] = 1;
+        s_counts[1] = 0;
+    }
+    __syncthreads();
     DescByKey comp{key};
-    while (sp > 0) {
-        --sp;
-        int first = stack_first[sp], last = stack_last[sp], depth = stack_depth[sp];
-        while (last - first > 16) {
+    int* qa = queue_a;
+    int* qb = queue_b;
+    for (;;) {
+        const int na = s_counts[0];
+        if (na == 0) break;
+        for (int r = warp; r < na; r += nwarps) {
+            const int e = qa[r];
+            const int first = e & 0xfff, last = (e >> 12) & 0x1fff;
+            int depth = e >> 25;
             if (depth == 0) {
                 if (lane == 0) iso_heap_sort(v, first, last, comp);
                 __syncwarp();
-                last = first;
-                break;
+                continue;
             }
             --depth;
-            const int mid = first + (last - first) / 2;
-            if (lane == 0) iso_move_median_to_first(v, first, first + 1, mid, last - 1, comp);
-            __syncwarp();
-            const int pk = key[v[first]];
-            const int lo = first + 1;
-            // left stops: key <= pivot key, ascending positions
-            int nL = 0;
-            for (int i0 = lo; i0 < last; i0 += 32) {
-                const int i = i0 + lane;
-                const bool a = i < last && key[v[i]] <= pk;
-                const unsigned bal = __ballot_sync(full, a);
-                if (a) lpos[nL + __popc(bal & ((1u << lane) - 1u))] = i;
-                nL += __popc(bal);
+            const int cut = warp_partition_desc(v, key, first, last, lpos + first, rpos + first, lane);
+            if (lane == 0) {
+                if (cut - first > 16) qb[atomicAdd(&s_counts[1], 1)] = first | (cut << 12) | (depth << 25);
+                if (last - cut > 16) qb[atomicAdd(&s_counts[1], 1)] = cut | (last << 12) | (depth << 25);
             }
-            // right stops: key >= pivot key, descending positions
-            int nR = 0;
-            for (int i0 = last - 1; i0 >= lo; i0 -= 32) {
-                const int i = i0 - lane;
-                const bool b = i >= lo && key[v[i]] >= pk;
-                const unsigned bal = __ballot_sync(full, b);
-                if (b) rpos[nR + __popc(bal & ((1u << lane) - 1u))] = i;
-                nR += __popc(bal);
-            }
-            __syncwarp();
-            const int nmin = nL < nR ? nL : nR;
-            int K = nmin;
-            for (int k0 = 0; k0 < nmin; k0 += 32) {
-                const int k = k0 + lane;
-                const bool cross = k < nmin && lpos[k] >= rpos[k];
-                const unsigned bal = __ballot_sync(full, cross);
-                if (bal) {
-                    K = k0 + __ffs(bal) - 1;
-                    break;
-                }
-            }
-            int cut = last;
-            if (K < nL) cut = lpos[K];
-            if (K >= 1 && rpos[K - 1] < cut) cut = rpos[K - 1];
-            for (int k = lane; k < K; k += 32) {
-                const int a = lpos[k], b = rpos[k];
-                const int t = v[a];
-                v[a] = v[b];
-                v[b] = t;
-            }
-            __syncwarp();
-            stack_first[sp] = cut; stack_last[sp] = last; stack_depth[sp] = depth; ++sp;
-            last = cut;
         }
+        __syncthreads();
+        if (tid == 0) {
+            s_counts[0] = s_counts[1];
+            s_counts[1] = 0;
+        }
+        int* t = qa;
+        qa = qb;
+        qb = t;
+        __syncthreads();
     }
 }
 #endif  // __CUDACC__

@@ -206,6 +206,29 @@ def test_set_mask_matches_reference_order(trackers, name):
         assert got.tolist() == ref.ids
 
 
+@pytest.mark.parametrize("name,cap,nmax,cluster", [("C1", 512, 500, False), ("C2", 256, 250, True), ("C4", 2016, 2000, False),
+                                                   ("C4", 2016, 1500, True)])
+def test_set_mask_paths(trackers, name, cap, nmax, cluster):
+    # cap <= 768: conflict bit matrix; cap > 768: neighbour lists; clustered points overflow the lists -> warp-serial greedy
+    c = _cfg(name)
+    rng = np.random.default_rng(11)
+    t = trackers(name, capacity=cap)
+    for trial in range(3):
+        n = int(rng.integers(nmax // 2, nmax + 1))
+        if cluster:
+            ctr = np.stack([rng.uniform(40, c["width"] - 40, 12), rng.uniform(40, c["height"] - 40, 12)], 1)
+            pts = ctr[rng.integers(0, 12, n)] + rng.normal(0, 6.0, (n, 2))
+            pts = np.clip(pts, 1, [c["width"] - 2, c["height"] - 2]).astype(np.float32)
+        else:
+            pts = np.stack([rng.uniform(1, c["width"] - 2, n), rng.uniform(1, c["height"] - 2, n)], 1).astype(np.float32)
+        cnt = rng.integers(2, 6, n).astype(np.int32)
+        ref = R.RefFeatureTracker(R.config_from_synth(c), ocam.from_config(c))
+        ref.next_pts, ref.ids, ref.track_cnt = pts.copy(), list(range(n)), cnt.tolist()
+        ref.set_mask()
+        got = t.stage_set_mask(pts, cnt)
+        assert got.tolist() == ref.ids
+
+
 @pytest.mark.parametrize("name", ["C1", "C2", "C3", "C4"])
 def test_undistort_parity(trackers, name):
     c = _cfg(name)

@@ -137,6 +137,13 @@ VS_API int vs_tracker_track(struct vs_tracker* t, const uint8_t* gray, int32_t s
 /* One frame for each of the handle's streams; frames[s] is an H x stride host image. */
 VS_API int vs_tracker_track_batch(struct vs_tracker* t, const uint8_t* const* frames, int32_t stride,
                            const double* time_s, vs_track_result* out /* [n_streams] */);
+/* Asynchronous form of vs_tracker_track_batch: submit enqueues upload + kernels + result download and returns at once;
+ * wait blocks until the OLDEST submitted batch is done and describes it in out[n_streams].  Up to two batches may be
+ * in flight, so the host->device copy of batch k+1 overlaps the kernels of batch k.  The frame buffers of a batch must
+ * stay valid until its wait returns; its results stay valid until the second wait after it. */
+VS_API int vs_tracker_submit_batch(struct vs_tracker* t, const uint8_t* const* frames, int32_t stride,
+                                   const double* time_s);
+VS_API int vs_tracker_wait(struct vs_tracker* t, vs_track_result* out /* [n_streams] */);
 /* Same, frames already resident in device memory: n_streams images, each H rows of `stride` bytes,
  * `image_stride_bytes` apart.  results_to_host = 0 leaves results on the device (fetch later). */
 VS_API int vs_tracker_track_batch_device(struct vs_tracker* t, const uint8_t* d_frames, int32_t stride,

@@ -53,7 +53,7 @@ REJECT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c
 EXPORTS = [
     "vs_last_error", "vs_abi_version", "vs_tracker_create", "vs_tracker_destroy",
     "vs_tracker_default_config", "vs_tracker_track", "vs_tracker_track_batch",
-    "vs_tracker_track_batch_device", "vs_tracker_fetch_results", "vs_tracker_set_params",
+    "vs_tracker_track_batch_device", "vs_tracker_submit_batch", "vs_tracker_wait", "vs_tracker_fetch_results", "vs_tracker_set_params",
     "vs_tracker_set_reject_callback", "vs_tracker_reset", "vs_tracker_launch_count",
     "vs_tracker_last_device_ms", "vs_stage_clahe", "vs_stage_pyramid", "vs_stage_lk",
     "vs_stage_min_eig", "vs_stage_good_features", "vs_stage_undistort", "vs_stage_set_mask",
@@ -89,6 +89,8 @@ def load():
     lib.vs_tracker_track_batch.argtypes = [vp, C.POINTER(vp), i32, C.POINTER(f64), C.POINTER(VsTrackResult)]
     lib.vs_tracker_track_batch_device.argtypes = [vp, vp, i32, i64, C.POINTER(f64), i32, C.POINTER(VsTrackResult)]
     lib.vs_tracker_fetch_results.argtypes = [vp, C.POINTER(VsTrackResult)]
+    lib.vs_tracker_submit_batch.argtypes = [vp, C.POINTER(vp), i32, C.POINTER(f64)]
+    lib.vs_tracker_wait.argtypes = [vp, C.POINTER(VsTrackResult)]
     lib.vs_tracker_set_params.argtypes = [vp, i32, i32, f64, i32, i32, i32, f64, f64]
     lib.vs_tracker_set_reject_callback.argtypes = [vp, REJECT_FN, vp]
     lib.vs_tracker_reset.argtypes = [vp, i32]

@@ -390,9 +390,11 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
         g.r_un = reinterpret_cast<float2*>(p); p += B * C * 8;
         g.r_vel = reinterpret_cast<float2*>(p);
     }
-    VS_TRY_CREATE(cudaMallocHost(&t->h_block, t->h_block_bytes));
-    memset(t->h_block, 0, t->h_block_bytes);
-    VS_TRY_CREATE(cudaMallocHost(&t->h_time, sizeof(double) * B));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_block, 2 * t->h_block_bytes));      // two result slots (submit / wait pipelining)
+    memset(t->h_block, 0, 2 * t->h_block_bytes);
+    VS_TRY_CREATE(cudaMallocHost(&t->h_time, 2 * sizeof(double) * B));
+    VS_TRY_CREATE(cudaEventCreateWithFlags(&t->ev_fetch[0], cudaEventDisableTiming));
+    VS_TRY_CREATE(cudaEventCreateWithFlags(&t->ev_fetch[1], cudaEventDisableTiming));
     VS_TRY_CREATE(cudaMallocHost(&t->h_wn, sizeof(int) * B));
     VS_TRY_CREATE(cudaMallocHost(&t->h_flag, sizeof(int) * B));
     VS_TRY_CREATE(cudaMallocHost(&t->h_lcur, sizeof(float2) * B * C));
@@ -453,6 +455,7 @@ void vs_tracker_destroy(vs_tracker* t) {
     for (vs_tracker* lane : t->lanes) vs_tracker_destroy(lane);
     t->lanes.clear();
     if (t->ev_done) cudaEventDestroy(t->ev_done);
+    for (int k = 0; k < 2; ++k) if (t->ev_fetch[k]) cudaEventDestroy(t->ev_fetch[k]);
     if (t->stream) cudaStreamSynchronize(t->stream);
     t->arena.release();
     if (t->d_eig) cudaFree(t->d_eig);
@@ -628,9 +631,9 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
     return VS_OK;
 }
 
-static void fill_results(vs_tracker* t, vs_track_result* out) {
+static void fill_results(vs_tracker* t, vs_track_result* out, int slot = 0) {
     const int64_t B = t->B, C = t->cap;
-    const uint8_t* p = t->h_block;
+    const uint8_t* p = t->h_block + (size_t)slot * t->h_block_bytes;
     const int* hdr = reinterpret_cast<const int*>(p); p += B * kHdrInts * 4;
     const int* ids = reinterpret_cast<const int*>(p); p += B * C * 4;
     const int* cnt = reinterpret_cast<const int*>(p); p += B * C * 4;
@@ -693,11 +696,12 @@ static int enqueue_upload(vs_tracker* t, const uint8_t* const* frames, int strid
 
 // one frame per stream, images resident on the device
 static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride, int64_t image_stride_bytes,
-                         const double* time_s) {
-    memcpy(t->h_time, time_s, sizeof(double) * t->B);
+                         const double* time_s, int slot = 0) {
+    double* h_time = t->h_time + (size_t)slot * t->B;
+    memcpy(h_time, time_s, sizeof(double) * t->B);
     VS_CUDA_TRY(cudaEventRecord(t->ev0, t->stream));
     prof_begin(t);
-    VS_CUDA_TRY(cudaMemcpyAsync(t->d_cur_time, t->h_time, sizeof(double) * t->B, cudaMemcpyHostToDevice, t->stream));
+    VS_CUDA_TRY(cudaMemcpyAsync(t->d_cur_time, h_time, sizeof(double) * t->B, cudaMemcpyHostToDevice, t->stream));
     const uint8_t* img = d_frames;
     int pitch = stride;
     int64_t istride = image_stride_bytes;
@@ -717,8 +721,10 @@ static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride,
     return VS_OK;
 }
 
-static int enqueue_fetch(vs_tracker* t) {
-    VS_CUDA_TRY(cudaMemcpyAsync(t->h_block, t->d_rblock, t->h_block_bytes, cudaMemcpyDeviceToHost, t->stream));
+static int enqueue_fetch(vs_tracker* t, int slot = 0) {
+    VS_CUDA_TRY(cudaMemcpyAsync(t->h_block + (size_t)slot * t->h_block_bytes, t->d_rblock, t->h_block_bytes,
+                                cudaMemcpyDeviceToHost, t->stream));
+    VS_CUDA_TRY(cudaEventRecord(t->ev_fetch[slot], t->stream));
     return VS_OK;
 }
 
@@ -763,6 +769,7 @@ int vs_tracker_fetch_results(vs_tracker* t, vs_track_result* out) {
 int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_t stride, int64_t image_stride_bytes,
                                   const double* time_s, int32_t results_to_host, vs_track_result* out) {
     if (!t || !d_frames || !time_s) { set_error("null argument"); return VS_ERR_INVALID; }
+    if (t->submit_seq != t->wait_seq) { set_error("a submitted batch is still in flight: call vs_tracker_wait first"); return VS_ERR_STATE; }
     if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
     VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
     if (!t->lanes.empty()) {
@@ -796,6 +803,7 @@ int vs_tracker_track_batch_device(vs_tracker* t, const uint8_t* d_frames, int32_
 int vs_tracker_track_batch(vs_tracker* t, const uint8_t* const* frames, int32_t stride, const double* time_s,
                            vs_track_result* out) {
     if (!t || !frames || !time_s || !out) { set_error("null argument"); return VS_ERR_INVALID; }
+    if (t->submit_seq != t->wait_seq) { set_error("a submitted batch is still in flight: call vs_tracker_wait first"); return VS_ERR_STATE; }
     if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
     VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
     if (!t->lanes.empty()) {
@@ -824,6 +832,51 @@ int vs_tracker_track_batch(vs_tracker* t, const uint8_t* const* frames, int32_t 
     int rc = enqueue_upload(t, frames, stride);
     if (rc != VS_OK) return rc;
     return vs_tracker_track_batch_device(t, t->d_raw, t->raw_pitch, t->raw_stride, time_s, 1, out);
+}
+
+// ---- asynchronous pair: up to two batches in flight, so the upload of batch k+1 overlaps the kernels of batch k ----
+int vs_tracker_submit_batch(vs_tracker* t, const uint8_t* const* frames, int32_t stride, const double* time_s) {
+    if (!t || !frames || !time_s) { set_error("null argument"); return VS_ERR_INVALID; }
+    if (stride < t->W) { set_error("stride < width"); return VS_ERR_INVALID; }
+    if (t->submit_seq - t->wait_seq >= 2) { set_error("two batches already in flight: call vs_tracker_wait first"); return VS_ERR_STATE; }
+    if (t->cfg.ransac_mode == VS_RANSAC_CALLBACK) { set_error("submit/wait is not available with VS_RANSAC_CALLBACK"); return VS_ERR_STATE; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    const int slot = (int)(t->submit_seq & 1);
+    if (!t->lanes.empty()) {
+        for (size_t l = 0; l < t->lanes.size(); ++l) {
+            vs_tracker* lane = t->lanes[l];
+            const int s0 = t->lane_s0[l];
+            int rc = enqueue_upload(lane, frames + s0, stride);
+            if (rc == VS_OK) rc = enqueue_frame(lane, lane->d_raw, lane->raw_pitch, lane->raw_stride, time_s + s0, slot);
+            if (rc == VS_OK) rc = enqueue_fetch(lane, slot);
+            if (rc != VS_OK) return rc;
+        }
+    } else {
+        int rc = enqueue_upload(t, frames, stride);
+        if (rc == VS_OK) rc = enqueue_frame(t, t->d_raw, t->raw_pitch, t->raw_stride, time_s, slot);
+        if (rc == VS_OK) rc = enqueue_fetch(t, slot);
+        if (rc != VS_OK) return rc;
+    }
+    ++t->submit_seq;
+    return VS_OK;
+}
+
+int vs_tracker_wait(vs_tracker* t, vs_track_result* out) {
+    if (!t || !out) { set_error("null argument"); return VS_ERR_INVALID; }
+    if (t->submit_seq == t->wait_seq) { set_error("vs_tracker_wait: nothing in flight"); return VS_ERR_STATE; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    const int slot = (int)(t->wait_seq & 1);
+    if (!t->lanes.empty()) {
+        for (size_t l = 0; l < t->lanes.size(); ++l) {
+            VS_CUDA_TRY(cudaEventSynchronize(t->lanes[l]->ev_fetch[slot]));
+            fill_results(t->lanes[l], out + t->lane_s0[l], slot);
+        }
+    } else {
+        VS_CUDA_TRY(cudaEventSynchronize(t->ev_fetch[slot]));
+        fill_results(t, out, slot);
+    }
+    ++t->wait_seq;
+    return VS_OK;
 }
 
 int vs_tracker_track(vs_tracker* t, const uint8_t* gray, int32_t stride, double time_s, vs_track_result* out) {

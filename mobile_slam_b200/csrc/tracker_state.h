@@ -92,5 +92,7 @@ struct vs_tracker {
     std::vector<vs_tracker*> lanes;
     std::vector<int> lane_s0;
     cudaEvent_t ev_done = nullptr;    // recorded on `stream` after the lane's last kernel (join)
+    cudaEvent_t ev_fetch[2] = {nullptr, nullptr};   // result slot k downloaded
+    int64_t submit_seq = 0, wait_seq = 0;            // vs_tracker_submit_batch / vs_tracker_wait
 };
 

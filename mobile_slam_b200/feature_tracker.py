@@ -181,6 +181,24 @@ class BatchTracker:
         _abi.check(self._lib.vs_tracker_track_batch(self._h, ptrs, self.tc.col, times_ctypes, self._res))
         return self._collect() if collect else None
 
+    def submit_pinned(self, base_ptr: int, image_stride: int, times_ctypes):
+        """Asynchronous track_pinned: returns at once; pair with wait() (at most two submits in flight)."""
+        ptrs = (C.c_void_p * self.n_streams)(*[base_ptr + s * image_stride for s in range(self.n_streams)])
+        _abi.check(self._lib.vs_tracker_submit_batch(self._h, ptrs, self.tc.col, times_ctypes))
+
+    def submit(self, frames, times):
+        fr = [np.ascontiguousarray(f, np.uint8) for f in frames]
+        self._inflight = getattr(self, "_inflight", []) + [fr]          # keep the buffers alive until wait()
+        ptrs = (C.c_void_p * self.n_streams)(*[f.ctypes.data for f in fr])
+        ts = (C.c_double * self.n_streams)(*[float(t) for t in times])
+        _abi.check(self._lib.vs_tracker_submit_batch(self._h, ptrs, self.tc.col, ts))
+
+    def wait(self, collect: bool = True):
+        _abi.check(self._lib.vs_tracker_wait(self._h, self._res))
+        if getattr(self, "_inflight", None):
+            self._inflight.pop(0)
+        return self._collect() if collect else None
+
     def track_device(self, d_ptr: int, stride: int, image_stride: int, times, to_host: bool = True,
                      collect: bool = True):
         ts = times if isinstance(times, C.Array) else (C.c_double * self.n_streams)(*[float(t) for t in times])

@@ -185,3 +185,67 @@ def test_sequence_device_ransac_statistical_parity(built_lib):
     assert np.mean(rej) < 0.10, f"device RANSAC rejects {np.mean(rej):.3f} of the tracked points per frame"
     assert abs(np.mean(pub_g[2:]) - np.mean(pub_r[2:])) <= 0.05 * np.mean(pub_r[2:]), (np.mean(pub_g), np.mean(pub_r))
     bt.close()
+
+
+def test_forward_backward_check(built_lib):
+    # north_star: LK "with the forward/backward consistency check" (fb_check = 1; the reference itself tracks forward only).
+    # Oracle: cv2 forward LK, cv2 backward LK from the forward result, keep |back - start| <= fb_threshold.
+    cfg = CONFIGS["C2"]
+    st = SynthStream(41, cfg["width"], cfg["height"], motion=3.0)
+    f0, f1 = st.frame(10), st.frame(11)
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, fb_check=1, fb_threshold=0.05)
+    bt = BatchTracker(tc, cam, 1)
+    r0 = bt.track([f0], [0.0])[0]
+    r1 = bt.track([f1], [0.05])[0]
+    clahe = cv2.createCLAHE(3.0, (8, 8))
+    e0, e1 = clahe.apply(f0), clahe.apply(f1)
+    crit = (cv2.TERM_CRITERIA_COUNT | cv2.TERM_CRITERIA_EPS, 30, 0.01)
+    p0 = r0.cur_pts.reshape(-1, 1, 2)
+    fwd, s1, _ = cv2.calcOpticalFlowPyrLK(e0, e1, p0, None, winSize=(21, 21), maxLevel=3, criteria=crit)
+    bwd, s2, _ = cv2.calcOpticalFlowPyrLK(e1, e0, fwd, None, winSize=(21, 21), maxLevel=3, criteria=crit)
+    fwd, bwd = fwd.reshape(-1, 2), bwd.reshape(-1, 2)
+    x, y = np.rint(fwd[:, 0]), np.rint(fwd[:, 1])
+    inb = (x >= 1) & (x < cfg["width"] - 1) & (y >= 1) & (y < cfg["height"] - 1)
+    d2 = ((bwd - r0.cur_pts) ** 2).sum(1)
+    keep = (s1.reshape(-1) == 1) & inb & (s2.reshape(-1) == 1) & (d2 <= 0.05 ** 2)
+    margin = np.abs(np.sqrt(d2) - 0.05) < 2e-3          # points whose round trip sits on the threshold may flip
+    want = set(r0.ids[keep & ~margin].tolist())
+    forbid = set(r0.ids[~keep & ~margin].tolist())
+    got = set(r1.ids[r1.track_cnt >= 2].tolist())
+    assert want <= got and not (forbid & got), (len(want), len(got), len(forbid & got))
+    assert 0 < (~keep).sum() < len(keep), "test input must reject some but not all points"
+    assert r1.counters["n_lk_ok"] == len(got)
+    bt.close()
+
+
+def test_submit_wait_matches_synchronous_calls(built_lib):
+    # two batches in flight (vs_tracker_submit_batch / vs_tracker_wait) return exactly the synchronous results, in order
+    cfg = CONFIGS["C1"]
+    S = 5
+    streams = [SynthStream(500 + s, cfg["width"], cfg["height"]) for s in range(S)]
+    frames = [np.stack([st.frame(k) for st in streams]) for k in range(7)]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, pipeline_lanes=2)
+    a, b = BatchTracker(tc, cam, S), BatchTracker(tc, cam, S)
+    ref = [a.track(list(frames[k]), [0.05 * k] * S) for k in range(7)]
+    got = []
+    b.submit(list(frames[0]), [0.0] * S)
+    for k in range(1, 7):
+        b.submit(list(frames[k]), [0.05 * k] * S)
+        got.append(b.wait())
+    got.append(b.wait())
+    for k in range(7):
+        for s in range(S):
+            assert ref[k][s].ids.tolist() == got[k][s].ids.tolist() and np.array_equal(ref[k][s].cur_pts, got[k][s].cur_pts)
+            assert np.array_equal(ref[k][s].pts_velocity, got[k][s].pts_velocity)
+    # protocol errors are reported, not ignored
+    from mobile_slam_b200 import VsError
+    with pytest.raises(VsError):
+        b.wait()
+    b.submit(list(frames[0]), [1.0] * S)
+    b.submit(list(frames[1]), [1.05] * S)
+    with pytest.raises(VsError):
+        b.submit(list(frames[2]), [1.1] * S)
+    with pytest.raises(VsError):
+        b.track(list(frames[2]), [1.1] * S)
+    b.wait(); b.wait()
+    a.close(); b.close()

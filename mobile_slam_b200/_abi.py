@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvs_tracker.so")
+LIB_PATH = os.environ.get("VS_TRACKER_LIB") or os.path.join(_HERE, "libvs_tracker.so")   # override: A/B builds of the same ABI
 
 VS_OK = 0
 VS_RANSAC_OFF, VS_RANSAC_DEVICE, VS_RANSAC_CALLBACK = 0, 1, 2

@@ -12,7 +12,7 @@
 namespace vs {
 
 constexpr int kLkMargin = 5;          // search tile = window + 2*margin
-constexpr int kLkWarpsPerCta = 8;
+constexpr int kLkWarpsPerCta = 4;
 
 __host__ __device__ inline int lk_tile_size(int win) { return win + 1 + 2 * kLkMargin; }
 __host__ __device__ inline int lk_tile_pitch(int win) { return (lk_tile_size(win) + 3) & ~3; }
@@ -506,7 +506,7 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
 // feature -> warp map leaves CTAs waiting for their slowest warp.  Every warp instead pulls the next
 // (stream, slot) work item from a global counter until the batch is drained.  Two counters alternate between
 // launches: launch k drains counter k&1 and clears the other one for launch k+1 (stream order makes that safe).
-__global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_fast21_kernel(LkParams p, int n_streams, int max_features,
+__global__ void __launch_bounds__(32 * kLkWarpsPerCta, 5) lk_fast21_kernel(LkParams p, int n_streams, int max_features,
                                                                         int* counters, int which) {
     __shared__ __align__(16) uint32_t s_tiles[kLkWarpsPerCta][kFastWarpSmem / 4];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

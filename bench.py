@@ -579,7 +579,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
-    ap.add_argument("--streams", type=int, default=256, help="camera streams per GPU")
+    ap.add_argument("--streams", type=int, default=512, help="camera streams per GPU")
     ap.add_argument("--ransac", type=int, default=0)
     ap.add_argument("--lanes", type=int, default=4, help="pipeline lanes of the e2e (host-frame) handle")
     ap.add_argument("--dev-lanes", type=int, default=1, help="pipeline lanes of the device-resident handle")

@@ -531,6 +531,19 @@ def run_ours(args, rank, world, local_rank):
         roofline = {"kernel": dom, "bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
                     "traffic": None, "peak_source": peak_src}
     frame_frac = alg["frame"] * value / 1e9 / peak
+    # measured DRAM traffic of the dominant kernel (one `ncu --set full` capture, committed under profiles/): per-stream
+    # bytes of that capture x the streams of this launch.  Only valid for the workload the capture was taken on.
+    try:
+        import glob
+        tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))
+        if tfiles and args.config == "C2":
+            tj = json.load(open(tfiles[-1]))
+            tk = tj["kernels"].get(dom_stage)
+            if tk:
+                roofline["traffic"] = tk["dram_bytes_per_stream"] * S
+                roofline["traffic_source"] = os.path.basename(tfiles[-1])
+    except Exception:  # noqa: BLE001 - the roofline stands without it
+        pass
 
     # ---- CPU baseline on this box's host cores (bounded sample) ----
     cpu = None

@@ -415,7 +415,9 @@ void launch_clahe_lut_only(const uint8_t* src, int src_pitch, int64_t src_stride
     // a thread of the private-counter kernel may see up to 4 * ceil(words/NT) pixels; keep that below 256
     const int words = ((g.tw + 6) / 4 + 1) * g.th;
     // fewest private copies that fit the byte counters: the merge costs 64 shared-memory reads per copy
-    if (exact_tiles && 4 * ((words + 31) / 32) <= 255) launch_lut_nt<32>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    // (with only a few streams the launch is latency-bound: spread a tile over more threads instead)
+    if (exact_tiles && n_streams >= 8 && 4 * ((words + 31) / 32) <= 255) launch_lut_nt<32>(src, src_pitch, src_stride, g, n_streams, luts, st);
+    else if (exact_tiles && n_streams < 8 && 4 * ((words + 127) / 128) <= 255) launch_lut_nt<128>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else if (exact_tiles && 4 * ((words + 63) / 64) <= 255) launch_lut_nt<64>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else if (exact_tiles && 4 * ((words + 127) / 128) <= 255) launch_lut_nt<128>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else if (exact_tiles && 4 * ((words + 255) / 256) <= 255 && area < 65536) launch_lut_nt<256>(src, src_pitch, src_stride, g, n_streams, luts, st);

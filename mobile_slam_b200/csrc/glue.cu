@@ -37,11 +37,10 @@ __device__ __forceinline__ int block_compact_slot(bool ok, int tid, int* s_warp_
     return slot;
 }
 
-__global__ void __launch_bounds__(256) post_lk_kernel(GlueParams g) {
+__device__ __forceinline__ void post_lk_body(const GlueParams& g, const int s, const int tid) {
     __shared__ int s_warp_cnt[8];
     __shared__ double s_red[8];
     __shared__ int s_flag;
-    const int s = blockIdx.x, tid = threadIdx.x;
     const int64_t o = (int64_t)s * g.cap;
     const int n = g.n[s];
     int base = 0;
@@ -144,8 +143,9 @@ __device__ __forceinline__ void bitonic_sort_desc_u64(unsigned long long* v, int
     }
 }
 
-__global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
-    extern __shared__ __align__(16) uint8_t dsm[];
+__global__ void __launch_bounds__(256) post_lk_kernel(GlueParams g) { post_lk_body(g, blockIdx.x, threadIdx.x); }
+
+__device__ __forceinline__ void set_mask_body(const GlueParams& g, const int s, const int tid, uint8_t* dsm) {
     unsigned long long* ck = reinterpret_cast<unsigned long long*>(dsm);   // (key, position) sort keys
     int* src = reinterpret_cast<int*>(ck + pow2_at_least(g.cap));          // surviving work indices (order preserved)
     int* key = src + g.cap;                          // track_cnt of src[j]
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
     __shared__ int s_warp_cnt[8];
     __shared__ int s_kn, s_overflow;
     __shared__ int s_isort[2];
-    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const int lane = tid & 31;
     const int64_t o = (int64_t)s * g.cap;
     const int wn = g.wn[s];
     const bool filt = g.ransac_flag[s] != 0;
@@ -449,6 +449,20 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
     }
 }
 
+__global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
+    extern __shared__ __align__(16) uint8_t dsm[];
+    set_mask_body(g, blockIdx.x, threadIdx.x, dsm);
+}
+
+// post_lk + set_mask in one launch (no RANSAC stage between them): both are one CTA per stream, and a CTA only
+// consumes what it wrote itself, so a block barrier is all the ordering needed
+__global__ void __launch_bounds__(256) post_lk_set_mask_kernel(GlueParams g) {
+    extern __shared__ __align__(16) uint8_t dsm[];
+    post_lk_body(g, blockIdx.x, threadIdx.x);
+    __syncthreads();
+    set_mask_body(g, blockIdx.x, threadIdx.x, dsm);
+}
+
 // ---------------------------------------------------------------------------------------------
 // K7: second half of cv::goodFeaturesToTrack — threshold 0.01 * max, order (eig desc, address desc),
 // greedy min-distance accept until `want` corners — then the rest of the frame: addPoints, updateID,
@@ -674,14 +688,16 @@ void launch_post_lk(const GlueParams& g, cudaStream_t st, int64_t* launches) {
     if (launches) *launches += 1;
 }
 
-void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches) {
+void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bool with_post_lk) {
     const int smem = set_mask_smem_bytes(g.cap);
     static int configured = 0;
     if (smem > 48 * 1024 && configured < smem) {
         cudaFuncSetAttribute(set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(post_lk_set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
+    if (with_post_lk) post_lk_set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
+    else set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
     if (launches) *launches += 1;
 }
 

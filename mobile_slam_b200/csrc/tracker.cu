@@ -608,8 +608,11 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
             prof_tick(t, PK_LK_BACK);
         }
     }
-    launch_post_lk(g, t->stream, &t->launches);
-    prof_tick(t, PK_POST_LK);
+    const bool fuse_glue = t->cfg.ransac_mode == VS_RANSAC_OFF;     // post_lk + set_mask in one launch
+    if (!fuse_glue) {
+        launch_post_lk(g, t->stream, &t->launches);
+        prof_tick(t, PK_POST_LK);
+    }
     if (t->cfg.ransac_mode == VS_RANSAC_CALLBACK) {
         const int rc = ransac_callback_hop(t);
         if (rc != VS_OK) return rc;
@@ -617,8 +620,8 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
         const int rc = launch_ransac(t);
         if (rc != VS_OK) return rc;
     }
-    prof_tick(t, PK_RANSAC);
-    launch_set_mask(g, t->stream, &t->launches);
+    if (!fuse_glue) prof_tick(t, PK_RANSAC);
+    launch_set_mask(g, t->stream, &t->launches, fuse_glue);
     prof_tick(t, PK_SET_MASK);
     StParams e = make_st_params(t, nb, g);
     launch_shi_tomasi(e, t->B, t->stream, &t->launches);
@@ -701,7 +704,7 @@ static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride,
     memcpy(h_time, time_s, sizeof(double) * t->B);
     VS_CUDA_TRY(cudaEventRecord(t->ev0, t->stream));
     prof_begin(t);
-    VS_CUDA_TRY(cudaMemcpyAsync(t->d_cur_time, h_time, sizeof(double) * t->B, cudaMemcpyHostToDevice, t->stream));
+    t->g.cur_time = h_time;      // pinned host memory is device-addressable (UVA): select_finish reads the B doubles in place
     const uint8_t* img = d_frames;
     int pitch = stride;
     int64_t istride = image_stride_bytes;
@@ -1121,6 +1124,7 @@ int vs_stage_good_features(vs_tracker* t, const uint8_t* img, const float* kept_
     g1.n_streams = 1;
     double zero = 0.0;
     VS_CUDA_TRY(cudaMemcpyAsync(t->d_cur_time, &zero, sizeof(double), cudaMemcpyHostToDevice, t->stream));
+    g1.cur_time = t->d_cur_time;
     launch_select_finish(g1, t->stream, &t->launches);
     int hdr[kHdrInts];
     VS_CUDA_TRY(cudaMemcpyAsync(hdr, g1.r_hdr, sizeof(hdr), cudaMemcpyDeviceToHost, t->stream));

@@ -267,13 +267,19 @@ __device__ __forceinline__ float round_magic(float r) {   // round-half-even of 
     return __fadd_rn(r, 12582912.0f);
 }
 
-// blockDim.x = 32 * (number of 128-column chunks): warp w owns columns 128w .. 128w+127 of the band
+// blockDim.x = 32 * (number of 256-column chunks): warp w owns columns 256w .. 256w+255 of the band and every lane
+// 8 consecutive pixels of a row (one 64-bit load / store).  The four LUT values a pixel blends are kept as 4 x fp16 per
+// (cell column, pixel value) in shared memory — one 64-bit load per pixel (a float4 table halves the instruction count
+// of the unpack but doubles the shared-memory wavefronts and was measured slower) — the horizontal weights are lane
+// constants, the vertical weights of the band's rows sit in a small shared table.
+constexpr int kApplyMaxBandRows = 512;
 __global__ void __launch_bounds__(1024) clahe_apply_kernel(const uint8_t* __restrict__ src, int src_pitch,
                                                            int64_t src_stride, uint8_t* __restrict__ dst,
                                                            int dst_pitch, int64_t dst_stride, int W, int H,
                                                            float inv_tw, float inv_th, ClaheBands bands,
                                                            const uint8_t* __restrict__ luts) {
-    __shared__ __align__(16) uint2 s_cell[kApplyCells][256];     // (p1, p2, q1, q2) as 4 x fp16
+    __shared__ __align__(16) uint2 s_cell[kApplyCells][256];         // (p1, p2 | q1, q2) as 4 x fp16 (bytes are exact in fp16)
+    __shared__ float2 s_ya[kApplyMaxBandRows];                        // (ya1, ya) of the CTA's rows
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int s = blockIdx.y;
     const int band = blockIdx.x / kApplyRowSplit, part = blockIdx.x - band * kApplyRowSplit;
@@ -294,63 +300,82 @@ __global__ void __launch_bounds__(1024) clahe_apply_kernel(const uint8_t* __rest
                                            __ushort2half_rn(L[(ty2 * kClaheTiles + tx2) * 256 + v]));
         s_cell[c][v] = make_uint2(*reinterpret_cast<const uint32_t*>(&top), *reinterpret_cast<const uint32_t*>(&bot));
     }
+    for (int r = tid; r < y_end - y_begin && r < kApplyMaxBandRows; r += blockDim.x) {
+        const float tyf = __fsub_rn(__fmul_rn((float)(y_begin + r), inv_th), 0.5f);
+        const float ya = __fsub_rn(tyf, floorf(tyf));
+        s_ya[r] = make_float2(__fsub_rn(1.0f, ya), ya);
+    }
     __syncthreads();
-    const int nchunks = (W + 127) >> 7, nwarps = blockDim.x >> 5;
-    const char* cells = reinterpret_cast<const char*>(&s_cell[0][0]);
-    for (int chunk = warp; chunk < nchunks; chunk += nwarps) {
-    // per-lane column constants: word x = 128*chunk + 4*lane
-    const int x = 128 * chunk + 4 * lane;
-    float xa[4], xa1[4];
-    uint32_t cell_off[4];                                            // byte offset of the pixel's cell table
+    const bool ya_tab = (y_end - y_begin) <= kApplyMaxBandRows;
+    const int nchunks = (W + 255) >> 8, nwarps = blockDim.x >> 5;
+    const uint32_t cells = (uint32_t)__cvta_generic_to_shared(&s_cell[0][0]);
+    // work unit = (256-column chunk, row group): a CTA carries >= 8 warps to amortise its table build; with few chunks
+    // per row the warps interleave over row pairs
+    const int rgroups = max(1, nwarps / nchunks);
+    for (int unit = warp; unit < nchunks * rgroups; unit += nwarps) {
+        const int chunk = unit % nchunks, rg = unit / nchunks;
+        const int x = 256 * chunk + 8 * lane;
+        if (x >= W) continue;
+        float xa[8], xa1[8];
+        uint32_t cell_addr[8];                                       // shared-memory address of the pixel's cell table
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float txf = __fsub_rn(__fmul_rn((float)(x + k), inv_tw), 0.5f);
-        const int tx1r = (int)floorf(txf);
-        xa[k] = __fsub_rn(txf, (float)tx1r);
-        xa1[k] = __fsub_rn(1.0f, xa[k]);
-        cell_off[k] = (uint32_t)min(max(tx1r + 1, 0), kApplyCells - 1) * (256u * 8u);
-    }
-    if (x >= W) continue;
-    const uint8_t* img = src + (int64_t)s * src_stride + x;
-    uint8_t* out = dst + (int64_t)s * dst_stride + x;
-    const bool full = (x + 3 < W);
-    auto fetch = [&](int y) -> uint32_t {
-        if (y >= y_end) return 0u;
-        const uint8_t* sp = img + (int64_t)y * src_pitch;
-        if (full) return __ldg(reinterpret_cast<const uint32_t*>(sp));
-        uint32_t v4 = 0;
-        for (int k = 0; k < 4 && x + k < W; ++k) v4 |= (uint32_t)sp[k] << (8 * k);
-        return v4;
-    };
-    auto process = [&](int y, uint32_t v4) {
-        if (y >= y_end) return;
-        const float tyf = __fsub_rn(__fmul_rn((float)y, inv_th), 0.5f);
-        const float ya = __fsub_rn(tyf, floorf(tyf)), ya1 = __fsub_rn(1.0f, ya);
-        uint32_t o4 = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint2 ent = *reinterpret_cast<const uint2*>(cells + cell_off[k] + ((v4 >> (8 * k)) & 255u) * 8u);
-            const float2 pt = __half22float2(*reinterpret_cast<const __half2*>(&ent.x));
-            const float2 pb = __half22float2(*reinterpret_cast<const __half2*>(&ent.y));
-            const float top = __fadd_rn(__fmul_rn(pt.x, xa1[k]), __fmul_rn(pt.y, xa[k]));
-            const float bot = __fadd_rn(__fmul_rn(pb.x, xa1[k]), __fmul_rn(pb.y, xa[k]));
-            const float r = __fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya));
-            // 0 <= r <= 255 (convex blend of bytes), so saturate_cast is the identity after rounding
-            o4 |= (__float_as_uint(round_magic(r)) & 255u) << (8 * k);
+        for (int k = 0; k < 8; ++k) {
+            const float txf = __fsub_rn(__fmul_rn((float)(x + k), inv_tw), 0.5f);
+            const int tx1r = (int)floorf(txf);
+            xa[k] = __fsub_rn(txf, (float)tx1r);
+            xa1[k] = __fsub_rn(1.0f, xa[k]);
+            cell_addr[k] = cells + (uint32_t)min(max(tx1r + 1, 0), kApplyCells - 1) * (256u * 8u);
         }
-        uint8_t* dp = out + (int64_t)y * dst_pitch;
-        if (full) *reinterpret_cast<uint32_t*>(dp) = o4;
-        else
-            for (int k = 0; k < 4 && x + k < W; ++k) dp[k] = (uint8_t)(o4 >> (8 * k));
-    };
-    for (int y = y_begin; y < y_end; y += 4) {
-        // four rows in flight per lane before the dependent table lookups
-        const uint32_t a0 = fetch(y), a1 = fetch(y + 1), a2 = fetch(y + 2), a3 = fetch(y + 3);
-        process(y, a0);
-        process(y + 1, a1);
-        process(y + 2, a2);
-        process(y + 3, a3);
-    }
+        const uint8_t* img = src + (int64_t)s * src_stride + x;
+        uint8_t* out = dst + (int64_t)s * dst_stride + x;
+        const bool full = (x + 7 < W);
+        auto fetch = [&](int y) -> uint2 {
+            if (y >= y_end) return make_uint2(0u, 0u);
+            const uint8_t* sp = img + (int64_t)y * src_pitch;
+            if (full) return __ldg(reinterpret_cast<const uint2*>(sp));
+            uint2 v = make_uint2(0u, 0u);
+            for (int k = 0; k < 8 && x + k < W; ++k) {
+                if (k < 4) v.x |= (uint32_t)sp[k] << (8 * k);
+                else v.y |= (uint32_t)sp[k] << (8 * (k - 4));
+            }
+            return v;
+        };
+        auto process = [&](int y, uint2 v8) {
+            if (y >= y_end) return;
+            float2 yw;
+            if (ya_tab) yw = s_ya[y - y_begin];
+            else {                                       // bands taller than the table (images above ~4K rows)
+                const float tyf = __fsub_rn(__fmul_rn((float)y, inv_th), 0.5f);
+                const float ya = __fsub_rn(tyf, floorf(tyf));
+                yw = make_float2(__fsub_rn(1.0f, ya), ya);
+            }
+            uint32_t o[2] = {0u, 0u};
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const uint32_t word = k < 4 ? v8.x : v8.y;
+                const uint32_t byte = __byte_perm(word, 0u, 0x4440u | (uint32_t)(k & 3));
+                uint2 ent;
+                asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ent.x), "=r"(ent.y) : "r"(cell_addr[k] + byte * 8u));
+                const float2 pt = __half22float2(*reinterpret_cast<const __half2*>(&ent.x));
+                const float2 pb = __half22float2(*reinterpret_cast<const __half2*>(&ent.y));
+                const float top = __fadd_rn(__fmul_rn(pt.x, xa1[k]), __fmul_rn(pt.y, xa[k]));
+                const float bot = __fadd_rn(__fmul_rn(pb.x, xa1[k]), __fmul_rn(pb.y, xa[k]));
+                const float r = __fadd_rn(__fmul_rn(top, yw.x), __fmul_rn(bot, yw.y));
+                // 0 <= r <= 255 (convex blend of bytes): the low byte of the magic-rounded float is the result
+                const uint32_t rb = __float_as_uint(round_magic(r));
+                o[k >> 2] = __byte_perm(o[k >> 2], rb, (k & 3) == 0 ? 0x3214u : (k & 3) == 1 ? 0x3240u : (k & 3) == 2 ? 0x3410u : 0x4210u);
+            }
+            uint8_t* dp = out + (int64_t)y * dst_pitch;
+            if (full) *reinterpret_cast<uint2*>(dp) = make_uint2(o[0], o[1]);
+            else
+                for (int k = 0; k < 8 && x + k < W; ++k) dp[k] = (uint8_t)(o[k >> 2] >> (8 * (k & 3)));
+        };
+        for (int y = y_begin + 2 * rg; y < y_end; y += 2 * rgroups) {
+            // two rows (16 pixels) in flight per lane before the dependent table lookups
+            const uint2 a0 = fetch(y), a1 = fetch(y + 1);
+            process(y, a0);
+            process(y + 1, a1);
+        }
     }   // chunk
 }
 
@@ -442,8 +467,9 @@ void launch_clahe_apply_only(const uint8_t* src, int src_pitch, int64_t src_stri
         while (b < cy + 1 && b < kClaheTiles) bands.start[++b] = y;
     }
     while (b < kClaheTiles + 1) bands.start[++b] = H;
-    const int nchunks = (W + 127) / 128;
-    const int nwarps = nchunks < 32 ? nchunks : 32;
+    const int nchunks = (W + 255) / 256;
+    int nwarps = nchunks < 32 ? nchunks : 32;
+    if (nwarps < 8) nwarps = (8 / nchunks) * nchunks;          // row groups fill the CTA up to 8 warps
     clahe_apply_kernel<<<dim3((kClaheTiles + 1) * kApplyRowSplit, n_streams), 32 * nwarps, 0, st>>>(
         src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, inv_tw, inv_th, bands, luts);
 }

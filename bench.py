@@ -338,6 +338,22 @@ def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     from mobile_slam_b200 import BatchTracker, VS_RANSAC_DEVICE, VS_RANSAC_OFF, config_from_synth
 
+    # NUMA: run this rank (and first-touch its pinned frame buffers) on the cores next to its GPU, otherwise every rank's
+    # host->device traffic crosses the socket interconnect from node 0
+    numa_cpus = None
+    orig_affinity = os.sched_getaffinity(0)
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        hnd = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            numa_cpus = len(cpus)
+    except Exception:  # noqa: BLE001 - affinity is an optimisation only
+        pass
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -548,6 +564,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- CPU baseline on this box's host cores (bounded sample) ----
     cpu = None
     if not args.no_cpu:
+        os.sched_setaffinity(0, orig_affinity)          # the CPU arm gets every host core back
         cores = os.cpu_count() or 1
         fps1, feats1, t1 = cpu_tracker_throughput(args.config, args.cpu_frames, 1, threads=1, use_ransac=bool(args.ransac))
         fpsN, featsN, tN = cpu_tracker_throughput(args.config, args.cpu_frames, cores, threads=1,
@@ -570,7 +587,7 @@ def run_ours(args, rank, world, local_rank):
         "features_per_s": value * pub_mean, "features_per_frame": pub_mean,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": step_bytes, "d2h_bytes_per_step": d2h_bytes,
                 "ms_per_step": 1e3 * e2e_s / K, "api": "vs_tracker_submit_batch / vs_tracker_wait, two batches in flight",
-                "sync_call_value": total_frames / e2e_sync_s, "h2d_link_gbs": h2d_gbs,
+                "sync_call_value": total_frames / e2e_sync_s, "h2d_link_gbs": h2d_gbs, "host_cpus_bound": numa_cpus,
                 "link_bound_frames_per_s": world * h2d_gbs * 1e9 / (H * W)},
         "gpu_launches": int(launches),
         "latency_us": lat,

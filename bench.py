@@ -324,7 +324,8 @@ def workload_config(args, cfg, streams):
     return {
         "workload": f"{args.config}: {cfg['width']}x{cfg['height']} mono, max_cnt {cfg['max_cnt']}, min_dist {cfg['min_dist']}, "
                     f"LK win {LK_WIN} maxLevel {cfg['max_level']} ({len(lv)} levels), camera {cfg['model']}",
-        "streams_per_gpu": streams, "ransac": "device" if args.ransac else "off (both arms)",
+        "streams_per_gpu": streams, "ransac": ("on: device 7-point RANSAC in this arm, cv2.findFundamentalMat in the CPU arms" if args.ransac
+                                              else "off (both arms)"),
         "e2e_pipeline_lanes": args.lanes,
         "parallelism": f"stream-sharded x{args.gpus}, no collective",
     }
@@ -487,19 +488,27 @@ def run_ours(args, rank, world, local_rank):
     # ---- (4) single-stream latency ----
     lat = None
     if rank == 0:
-        bt1 = BatchTracker(tc, cam, 1)
-        ts1 = []
-        n_lat = args.latency_frames
-        for i in range(n_lat + 5):
-            f = h_frames[bounce(i, n_buf), 0]
-            tt = (C.c_double * 1)(0.05 * i)
-            t0 = time.perf_counter()
-            bt1.track_pinned(f.data_ptr(), H * W, tt)
-            ts1.append(time.perf_counter() - t0)
-        ts1 = np.array(ts1[5:]) * 1e6
-        lat = {"p50": float(np.percentile(ts1, 50)), "p95": float(np.percentile(ts1, 95)),
-               "frames": n_lat, "device_ms_last": bt1.last_device_ms}
-        bt1.close()
+        def one_stream_latency(tc1):
+            bt1 = BatchTracker(tc1, cam, 1)
+            ts1 = []
+            n_lat = args.latency_frames
+            for i in range(n_lat + 5):
+                f = h_frames[bounce(i, n_buf), 0]
+                tt = (C.c_double * 1)(0.05 * i)
+                t0 = time.perf_counter()
+                bt1.track_pinned(f.data_ptr(), H * W, tt)
+                ts1.append(time.perf_counter() - t0)
+            ts1 = np.array(ts1[5:]) * 1e6
+            r = {"p50": float(np.percentile(ts1, 50)), "p95": float(np.percentile(ts1, 95)),
+                 "frames": n_lat, "device_ms_last": bt1.last_device_ms}
+            bt1.close()
+            return r
+        lat = one_stream_latency(tc)
+        if args.ransac:
+            # the same frames with the F-matrix rejection switched off: what the north_star's kernel list alone costs
+            tc_off, _ = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, device=local_rank)
+            tc_off.pipeline_lanes = tc.pipeline_lanes
+            lat["ransac_off_p50"] = one_stream_latency(tc_off)["p50"]
 
     total_frames = sum_over_ranks(float(S * K))
     value = total_frames / (dev_ms * 1e-3)
@@ -610,7 +619,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--streams", type=int, default=512, help="camera streams per GPU")
-    ap.add_argument("--ransac", type=int, default=0)
+    ap.add_argument("--ransac", type=int, default=1)
     ap.add_argument("--lanes", type=int, default=4, help="pipeline lanes of the e2e (host-frame) handle")
     ap.add_argument("--dev-lanes", type=int, default=1, help="pipeline lanes of the device-resident handle")
     ap.add_argument("--max-frames", type=int, default=32, help="distinct frames buffered per stream")

@@ -10,6 +10,7 @@
 #include "camera.cuh"
 #include "glue.cuh"
 #include "introsort.cuh"
+#include "ransac.cuh"
 
 namespace vs {
 
@@ -463,6 +464,17 @@ __global__ void __launch_bounds__(256) post_lk_set_mask_kernel(GlueParams g) {
     set_mask_body(g, blockIdx.x, threadIdx.x, dsm);
 }
 
+// ... and with the device F-matrix RANSAC between them (VS_RANSAC_DEVICE): still one CTA per stream end to end
+__global__ void __launch_bounds__(256) post_lk_ransac_set_mask_kernel(GlueParams g, unsigned int seed) {
+    extern __shared__ __align__(16) uint8_t dsm[];
+    static_assert(kRansacThreads == 256, "glue kernels run 256 threads per stream");
+    post_lk_body(g, blockIdx.x, threadIdx.x);
+    __syncthreads();
+    ransac_body(g, seed, blockIdx.x, threadIdx.x, dsm);
+    __syncthreads();
+    set_mask_body(g, blockIdx.x, threadIdx.x, dsm);
+}
+
 // ---------------------------------------------------------------------------------------------
 // K7: second half of cv::goodFeaturesToTrack — threshold 0.01 * max, order (eig desc, address desc),
 // greedy min-distance accept until `want` corners — then the rest of the frame: addPoints, updateID,
@@ -688,15 +700,19 @@ void launch_post_lk(const GlueParams& g, cudaStream_t st, int64_t* launches) {
     if (launches) *launches += 1;
 }
 
-void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bool with_post_lk) {
-    const int smem = set_mask_smem_bytes(g.cap);
+void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bool with_post_lk, bool with_ransac,
+                     unsigned int seed) {
+    int smem = set_mask_smem_bytes(g.cap);
+    if (with_ransac && smem < g.cap * 16) smem = g.cap * 16;
     static int configured = 0;
     if (smem > 48 * 1024 && configured < smem) {
         cudaFuncSetAttribute(set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         cudaFuncSetAttribute(post_lk_set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(post_lk_ransac_set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    if (with_post_lk) post_lk_set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
+    if (with_post_lk && with_ransac) post_lk_ransac_set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g, seed);
+    else if (with_post_lk) post_lk_set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
     else set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
     if (launches) *launches += 1;
 }

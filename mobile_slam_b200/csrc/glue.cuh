@@ -81,7 +81,9 @@ struct GlueParams {
 };
 
 void launch_post_lk(const GlueParams& g, cudaStream_t st, int64_t* launches);
-void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bool with_post_lk = false);
+// with_post_lk: post_lk fused in front; with_ransac (needs with_post_lk): device RANSAC fused between them
+void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bool with_post_lk = false,
+                     bool with_ransac = false, unsigned int seed = 0);
 void launch_select_finish(const GlueParams& g, cudaStream_t st, int64_t* launches);
 void launch_undistort(const CameraDev& cam, const float2* pts, int n, float2* out, cudaStream_t st);
 int set_mask_smem_bytes(int cap);

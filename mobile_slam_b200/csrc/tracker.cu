@@ -482,6 +482,7 @@ void vs_tracker_destroy(vs_tracker* t) {
 namespace vs {
 
 int launch_ransac(vs_tracker* t);   // ransac.cu
+static inline unsigned ransac_seed(const vs_tracker* t) { return (unsigned)(t->lk_seq * 2654435761u + 12345u); }
 
 static void fill_lk_params(vs_tracker* t, LkParams& p, int prev_buf, int next_buf, const float2* pts, float2* out,
                            uint8_t* status) {
@@ -608,7 +609,10 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
             prof_tick(t, PK_LK_BACK);
         }
     }
-    const bool fuse_glue = t->cfg.ransac_mode == VS_RANSAC_OFF;     // post_lk + set_mask in one launch
+    // post_lk (+ device RANSAC) + set_mask in one launch; the profiled pass keeps RANSAC as its own launch so that
+    // its share of the frame stays visible
+    const bool fuse_ransac = t->cfg.ransac_mode == VS_RANSAC_DEVICE && !t->prof.on;
+    const bool fuse_glue = t->cfg.ransac_mode == VS_RANSAC_OFF || fuse_ransac;
     if (!fuse_glue) {
         launch_post_lk(g, t->stream, &t->launches);
         prof_tick(t, PK_POST_LK);
@@ -616,12 +620,12 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
     if (t->cfg.ransac_mode == VS_RANSAC_CALLBACK) {
         const int rc = ransac_callback_hop(t);
         if (rc != VS_OK) return rc;
-    } else if (t->cfg.ransac_mode == VS_RANSAC_DEVICE) {
+    } else if (t->cfg.ransac_mode == VS_RANSAC_DEVICE && !fuse_ransac) {
         const int rc = launch_ransac(t);
         if (rc != VS_OK) return rc;
     }
     if (!fuse_glue) prof_tick(t, PK_RANSAC);
-    launch_set_mask(g, t->stream, &t->launches, fuse_glue);
+    launch_set_mask(g, t->stream, &t->launches, fuse_glue, fuse_ransac, ransac_seed(t));
     prof_tick(t, PK_SET_MASK);
     StParams e = make_st_params(t, nb, g);
     launch_shi_tomasi(e, t->B, t->stream, &t->launches);

@@ -187,6 +187,34 @@ def test_sequence_device_ransac_statistical_parity(built_lib):
     bt.close()
 
 
+def test_device_ransac_fused_launch_matches_separate_launches(built_lib):
+    # VS_RANSAC_DEVICE normally runs post_lk + RANSAC + set_mask as ONE launch per frame; with profiling on the three
+    # stay separate launches.  Same per-frame seed, same arithmetic: results must be identical, frame by frame.
+    from mobile_slam_b200 import VS_RANSAC_DEVICE
+    cfg = CONFIGS["C1"]
+    S = 3
+    streams = [SynthStream(70 + s, cfg["width"], cfg["height"], motion=2.0) for s in range(S)]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_DEVICE)
+    fused, split = BatchTracker(tc, cam, S), BatchTracker(tc, cam, S)
+    split.set_profiling(True)
+    ran = 0
+    for k in range(12):
+        frames = [st.frame(k) for st in streams]
+        a = fused.track(frames, [0.05 * k] * S)
+        b = split.track(frames, [0.05 * k] * S)
+        for s in range(S):
+            assert a[s].ids.tolist() == b[s].ids.tolist() and a[s].track_cnt.tolist() == b[s].track_cnt.tolist()
+            assert np.array_equal(a[s].cur_pts, b[s].cur_pts)
+            assert a[s].counters["n_ransac_out"] == b[s].counters["n_ransac_out"]
+            ran += a[s].counters["ransac_ran"]
+    assert ran >= 15
+    prof = split.profile()
+    assert prof["ransac"][1] > 0 and prof["post_lk"][1] > 0
+    assert fused.launch_count < split.launch_count
+    fused.close()
+    split.close()
+
+
 def test_forward_backward_check(built_lib):
     # north_star: LK "with the forward/backward consistency check" (fb_check = 1; the reference itself tracks forward only).
     # Oracle: cv2 forward LK, cv2 backward LK from the forward result, keep |back - start| <= fb_threshold.

@@ -283,20 +283,29 @@ def _two_view(n, outlier_frac, seed, w=752, h=480, f=460.0, noise=0.15):
     return a.astype(np.float32), b.astype(np.float32), out
 
 
-@pytest.mark.parametrize("n,frac,seed", [(150, 0.2, 1), (150, 0.4, 2), (60, 0.1, 3), (400, 0.3, 4), (40, 0.0, 5)])
-def test_ransac_device_vs_cv(trackers, n, frac, seed):
-    a, b, outl = _two_view(n, frac, seed)
+@pytest.mark.parametrize("n,frac", [(150, 0.2), (150, 0.4), (60, 0.1), (400, 0.3), (40, 0.0)])
+def test_ransac_device_vs_cv(trackers, n, frac):
+    # RANSAC draws differ (OpenCV's RNG is internal), so single masks are noisy for BOTH implementations: cv2 against
+    # itself on a permutation of the same points agrees on 0.885 .. 0.95 of the flags.  The contract is
+    # therefore statistical, over an ensemble of two-view sets: the device keeps as many true inliers and rejects as
+    # many true outliers as cv2 does on average, and no single mask is far from cv2's.
     t = trackers("C2", capacity=512)
-    st = t.stage_ransac(a, b).astype(bool)
-    _, cvm = cv2.findFundamentalMat(a, b, cv2.FM_RANSAC, 1.0, 0.99)
-    cvm = cvm.reshape(-1).astype(bool)
-    inl = ~outl
-    assert st[inl].mean() >= min(0.95, cvm[inl].mean() - 0.03), f"true inliers kept {st[inl].mean():.3f} (cv {cvm[inl].mean():.3f})"
-    if outl.any():
-        # an outlier displaced along its epipolar line is undetectable for both; require what cv2 achieves -5 %
-        assert (~st[outl]).mean() >= (~cvm[outl]).mean() - 0.05
-    # noise floor: cv2 against ITSELF on a permutation of the same points (different RANSAC samples) agrees on
-    # 0.885 .. 0.95 of the flags for these inputs (measured), so 0.88 is "as close as cv2 is to cv2"
-    assert (st == cvm).mean() >= 0.88, f"mask agreement with cv2 {(st == cvm).mean():.3f}"
+    kept, kept_cv, rej, rej_cv, agree = [], [], [], [], []
+    for seed in range(16):
+        a, b, outl = _two_view(n, frac, 100 + seed)
+        st = t.stage_ransac(a, b).astype(bool)
+        _, cvm = cv2.findFundamentalMat(a, b, cv2.FM_RANSAC, 1.0, 0.99)
+        cvm = cvm.reshape(-1).astype(bool)
+        inl = ~outl
+        kept.append(st[inl].mean()); kept_cv.append(cvm[inl].mean())
+        if outl.any():
+            # an outlier displaced along its epipolar line is undetectable for both
+            rej.append((~st[outl]).mean()); rej_cv.append((~cvm[outl]).mean())
+        agree.append((st == cvm).mean())
+    assert np.mean(kept) >= np.mean(kept_cv) - 0.02, f"true inliers kept {np.mean(kept):.3f} (cv {np.mean(kept_cv):.3f})"
+    if rej:
+        assert np.mean(rej) >= np.mean(rej_cv) - 0.03, f"outliers rejected {np.mean(rej):.3f} (cv {np.mean(rej_cv):.3f})"
+    assert np.mean(agree) >= 0.90, f"mean mask agreement with cv2 {np.mean(agree):.3f}"
+    assert np.min(agree) >= 0.80, f"worst mask agreement with cv2 {np.min(agree):.3f}"
     # deterministic: same input, same mask
     assert np.array_equal(t.stage_ransac(a, b).astype(bool), st)

@@ -70,7 +70,14 @@ __device__ inline double kb_theta(const CameraDev& c, double r) {
     }
     bool ok = isfinite(t) && t >= -1e-10 && fabs(kb_poly(c, t, r)) <= 1e-9 * fmax(1.0, r);
     const double hi = ok ? t : fmax(4.0, 2.0 * r);
-    if (r > 0.0) {
+    // with a converged Newton root the scan below only matters if f already changed sign before it: test the 31
+    // interior nodes first (independent evaluations, unrolled), and walk them one by one only in that rare case
+    bool scan = !ok;
+    if (ok && r > 0.0) {
+#pragma unroll 8
+        for (int j = 1; j < 32; ++j) scan |= kb_poly(c, hi * (double)j / 32.0, r) >= 0.0;
+    }
+    if (r > 0.0 && scan) {
         double a = 0.0, fa = -r;   // f(0) = -r < 0
 #pragma unroll 1
         for (int j = 1; j <= 32; ++j) {

@@ -185,8 +185,18 @@ __device__ __forceinline__ void set_mask_body(const GlueParams& g, const int s, 
                                  ((unsigned long long)(0xFFFFu - (unsigned int)i) << 16) | (unsigned int)perm[i]
                            : 0ull;
         __syncthreads();
-        bitonic_sort_desc_u64(ck, N, tid, 256);
-        for (int i = tid; i < n2; i += 256) perm[i] = (int)(ck[i] & 0xFFFFull);
+        if (n2 <= 256) {
+            // one key per thread: its rank among the (unique) keys is its sorted position
+            if (tid < n2) {
+                const unsigned long long mine = ck[tid];
+                int rank = 0;
+                for (int i = 0; i < n2; ++i) rank += ck[i] > mine ? 1 : 0;
+                perm[rank] = (int)(mine & 0xFFFFull);
+            }
+        } else {
+            bitonic_sort_desc_u64(ck, N, tid, 256);
+            for (int i = tid; i < n2; i += 256) perm[i] = (int)(ck[i] & 0xFFFFull);
+        }
     }
     __syncthreads();
     if (n2 <= kFixedPointMax && g.cap <= kFixedPointMax) {
@@ -217,20 +227,21 @@ __device__ __forceinline__ void set_mask_body(const GlueParams& g, const int s, 
             }
         }
         __syncthreads();
-        for (int idx = tid; idx < n2 * nw; idx += 256) {
-            const int q = idx / nw, w = idx - q * nw;
-            uint32_t bits = 0;
-            const int a0 = 32 * w;
-            if (a0 < q) {
-                const int rx = acc[q].x, ry = acc[q].y;
-                const int na = min(32, q - a0);
-                for (int b = 0; b < na; ++b) {
-                    const short2 c = acc[a0 + b];
+        // a warp takes point q, its lanes the 32 earlier points of one word: one pair test per lane, ballot = the word
+        // (words above q >> 5 are never read by the sweeps)
+        for (int q = tid >> 5; q < n2; q += 8) {
+            const int rx = acc[q].x, ry = acc[q].y;
+            for (int w = 0; w <= (q >> 5); ++w) {
+                const int a = 32 * w + lane;
+                bool hit = false;
+                if (a < q) {
+                    const short2 c = acc[a];
                     const int dy = abs(ry - (int)c.y), dx = abs(rx - (int)c.x);
-                    if (dy <= R && dx <= __ldg(g.disc_hw + dy)) bits |= 1u << b;
+                    hit = dy <= R && dx <= __ldg(g.disc_hw + dy);
                 }
+                const unsigned bal = __ballot_sync(0xffffffffu, hit);
+                if (lane == 0) conf[q * nw + w] = bal;
             }
-            conf[idx] = bits;
         }
         __syncthreads();
         uint32_t* cur = kb0;
@@ -591,16 +602,32 @@ __global__ void __launch_bounds__(kFinishThreads) select_finish_kernel(GlueParam
         while (n_valid > 0) {
             __syncthreads();
             // highest bin boundary b such that bins >= b hold at least `target` keys (or everything)
-            if (tid == 0) {
-                int acc = 0, b = kSelBins - 1;
-                for (; b > 0; --b) {
-                    acc += hist[b];
-                    if (acc >= target) break;
+            if (tid < 32) {
+                // lane L owns bins [32 L, 32 L + 32); suffix sums over the lanes find the lane where the running
+                // total (from the top bin down) reaches `target`, that lane then walks its own 32 bins
+                static_assert(kSelBins == 1024, "one warp x 32 bins");
+                int part = 0;
+#pragma unroll 8
+                for (int b = 0; b < 32; ++b) part += hist[32 * lane + ((b + lane) & 31)];   // rotated: no bank conflicts
+                int suf = part;
+#pragma unroll
+                for (int o2 = 1; o2 < 32; o2 <<= 1) {
+                    const int t = __shfl_down_sync(0xffffffffu, suf, o2);
+                    if (lane + o2 < 32) suf += t;
                 }
-                if (b == 0) acc += hist[0];
-                s_bin = b;
-                s_cnt = 0;
-                s_total = acc;
+                const unsigned m = __ballot_sync(0xffffffffu, suf >= target);
+                if (m == 0) {                        // fewer than `target` keys in total: take everything
+                    if (lane == 0) { s_bin = 0; s_cnt = 0; s_total = suf; }
+                } else if (lane == 31 - __clz(m)) {
+                    int acc = suf - part, b = 32 * lane + 31;
+                    for (;; --b) {
+                        acc += hist[b];
+                        if (acc >= target || b == 32 * lane) break;
+                    }
+                    s_bin = b;
+                    s_cnt = 0;
+                    s_total = acc;
+                }
             }
             __syncthreads();
             const int bsel = s_bin, nsel = s_total;
@@ -626,7 +653,21 @@ __global__ void __launch_bounds__(kFinishThreads) select_finish_kernel(GlueParam
                 v = gk;
             }
             __syncthreads();
-            bitonic_sort_desc(v, N, tid, kFinishThreads);
+            if (v == skeys && nsel <= kFinishThreads) {
+                // the usual case (a few dozen keys): rank sort, one key per thread (keys are unique: the low word is
+                // the pixel address), instead of log^2 N barrier-separated bitonic stages
+                unsigned long long mine = 0ull;
+                int rank = 0;
+                if (tid < nsel) {
+                    mine = skeys[tid];
+                    for (int i = 0; i < nsel; ++i) rank += skeys[i] > mine ? 1 : 0;
+                }
+                __syncthreads();
+                if (tid < nsel) skeys[rank] = mine;
+                __syncthreads();
+            } else {
+                bitonic_sort_desc(v, N, tid, kFinishThreads);
+            }
             const int nv = (v == gk) ? n_valid : nsel;
             if (tid < 32) {
                 const int A = greedy_accept(v, nv, want, g.W, md2, newp, lane);

@@ -1,9 +1,9 @@
 """Single-stream latency probe: N frames of one synthetic stream through vs_tracker_track (host frame in, results out).
-usage: python scripts/latency_probe.py [C1|C2] [frames]"""
+usage: python scripts/latency_probe.py [C1|C2] [frames] [off]   (off = without the F-matrix RANSAC)"""
 import os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from mobile_slam_b200 import BatchTracker, VS_RANSAC_OFF, config_from_synth
+from mobile_slam_b200 import BatchTracker, VS_RANSAC_OFF, VS_RANSAC_DEVICE, config_from_synth
 from mobile_slam_b200.synth import CONFIGS, SynthStream
 import ctypes as C
 name = sys.argv[1] if len(sys.argv) > 1 else "C1"
@@ -11,7 +11,8 @@ n = int(sys.argv[2]) if len(sys.argv) > 2 else 60
 cfg = CONFIGS[name]
 st = SynthStream(77, cfg["width"], cfg["height"])
 frames = [st.frame(k) for k in range(24)]
-tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+mode = VS_RANSAC_OFF if (len(sys.argv) > 3 and sys.argv[3] == 'off') else VS_RANSAC_DEVICE
+tc, cam = config_from_synth(cfg, ransac_mode=mode)
 bt = BatchTracker(tc, cam, 1)
 ts, dev = [], []
 for i in range(n):

@@ -105,63 +105,69 @@ __device__ __forceinline__ void seven_point_group(const float2* pa, const float2
         A[r] = u * v;
         B[r] = 1.0;
     }
-    // reduced row echelon form with full pivoting: columns stay in place, pivot columns are remembered
-    int mystep = -1, bstep = -1;           // step at which my column / column 8 became the pivot column
-    unsigned pmask = 0;                    // columns used as pivots
+    // reduced row echelon form with full pivoting.  Rows and columns stay where they are; used pivot rows / columns
+    // are remembered in bit masks, so the step body does not depend on the step number and stays a rolled loop
+    // (small code: the solver runs once per round, straight-line code would be fetched cold every time)
+    int myrow = -1, brow = -1;             // row in which my column / column 8 is the pivot
+    unsigned pmask = 0, rmask = 0;         // columns / rows used as pivots
     bool ok = true;
     const unsigned tiny = (unsigned)__double2hiint(1e-12);
-#pragma unroll
+#pragma unroll 1
     for (int k = 0; k < 7; ++k) {
-        // arg-max |a| over the not yet reduced rows and columns; key = high word of |a| with (column, row) in
+        // arg-max |a| over the not yet used rows and columns; key = high word of |a| with (column, row) in
         // the low 7 bits (13 mantissa bits are plenty to pick a pivot)
         unsigned key = 0;
 #pragma unroll
-        for (int r = k; r < 7; ++r) {
+        for (int r = 0; r < 7; ++r) {
+            const bool rfree = ((rmask >> r) & 1u) == 0;
             const unsigned ca = ((unsigned)__double2hiint(fabs(A[r])) & ~0x7Fu) | (unsigned)(j << 3 | r);
             const unsigned cb = ((unsigned)__double2hiint(fabs(B[r])) & ~0x7Fu) | (unsigned)(8 << 3 | r);
-            key = max(key, mystep < 0 ? ca : 0u);
-            key = max(key, bstep < 0 ? cb : 0u);
+            key = max(key, (rfree && myrow < 0) ? ca : 0u);
+            key = max(key, (rfree && brow < 0) ? cb : 0u);
         }
         key = max(key, __shfl_xor_sync(FULL, key, 1));
         key = max(key, __shfl_xor_sync(FULL, key, 2));
         key = max(key, __shfl_xor_sync(FULL, key, 4));
         const int pr = key & 7, pc = (key >> 3) & 15;
         ok = ok && (key & ~0x7Fu) >= tiny;                  // rank deficient sample otherwise
-        double ak = A[k], bk = B[k];                        // bring the pivot row to position k
+        double ak = A[0], bk = B[0];                        // my elements of the pivot row
 #pragma unroll
-        for (int r = k + 1; r < 7; ++r)
-            if (pr == r) { ak = A[r]; bk = B[r]; A[r] = A[k]; B[r] = B[k]; }
+        for (int r = 1; r < 7; ++r)
+            if (pr == r) { ak = A[r]; bk = B[r]; }
         const int src = gbase + (pc & 7);
         double piv = __shfl_sync(FULL, ak, src);
         if (pc == 8) piv = bk;
         const double inv = 1.0 / piv;
         ak *= inv;
         bk *= inv;
-        A[k] = ak;
-        B[k] = bk;
 #pragma unroll
         for (int r = 0; r < 7; ++r) {
-            if (r == k) continue;
             double f = __shfl_sync(FULL, A[r], src);
             if (pc == 8) f = B[r];
-            A[r] -= f * ak;
-            B[r] -= f * bk;
+            if (r == pr) {
+                A[r] = ak;
+                B[r] = bk;
+            } else {
+                A[r] -= f * ak;
+                B[r] -= f * bk;
+            }
         }
-        if (pc == j) mystep = k;
-        if (pc == 8) bstep = k;
+        if (pc == j) myrow = pr;
+        if (pc == 8) brow = pr;
         pmask |= 1u << pc;
+        rmask |= 1u << pr;
     }
     // null space basis: the two columns that never became pivots are the free variables
     const unsigned fm = ~pmask & 0x1FFu;
     const int free1 = __ffs(fm) - 1, free2 = 31 - __clz(fm);        // free1 < free2, free1 <= 7
     double e1 = 0.0, e2 = 0.0, e81 = 0.0, e82 = 0.0;                // entries j and 8 of the two basis vectors
 #pragma unroll
-    for (int k = 0; k < 7; ++k) {
-        const double v1 = __shfl_sync(FULL, A[k], gbase + free1);
-        double v2 = __shfl_sync(FULL, A[k], gbase + (free2 & 7));
-        if (free2 == 8) v2 = B[k];
-        if (mystep == k) { e1 = -v1; e2 = -v2; }
-        if (bstep == k) { e81 = -v1; e82 = -v2; }
+    for (int r = 0; r < 7; ++r) {
+        const double v1 = __shfl_sync(FULL, A[r], gbase + free1);
+        double v2 = __shfl_sync(FULL, A[r], gbase + (free2 & 7));
+        if (free2 == 8) v2 = B[r];
+        if (myrow == r) { e1 = -v1; e2 = -v2; }
+        if (brow == r) { e81 = -v1; e82 = -v2; }
     }
     if (j == free1) { e1 = 1.0; e2 = 0.0; }
     if (j == free2) { e1 = 0.0; e2 = 1.0; }

@@ -24,6 +24,7 @@ template <int NT, bool FULLW>
 __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict__ src, int pitch, int64_t img_stride,
                                                        int tw, int th, int clip, float lut_scale,
                                                        uint8_t* __restrict__ luts) {
+    pdl_entry();
     extern __shared__ __align__(16) uint32_t s_cnt[];          // [64 word rows][NT threads]
     __shared__ uint32_t s_part[NT >= 64 ? NT / 64 : 1][64][2];
     __shared__ int s_hist[256];
@@ -193,6 +194,7 @@ __global__ void __launch_bounds__(256) clahe_lut_generic_kernel(const uint8_t* _
                                                                 int64_t img_stride, int W, int H, int tw, int th,
                                                                 int clip, float lut_scale,
                                                                 uint8_t* __restrict__ luts) {
+    pdl_entry();
     __shared__ unsigned int hist[8][256];
     __shared__ unsigned int warp_tot[8];
     __shared__ unsigned int s_clipped;
@@ -278,6 +280,7 @@ __global__ void __launch_bounds__(1024) clahe_apply_kernel(const uint8_t* __rest
                                                            int dst_pitch, int64_t dst_stride, int W, int H,
                                                            float inv_tw, float inv_th, ClaheBands bands,
                                                            const uint8_t* __restrict__ luts) {
+    pdl_entry();
     __shared__ __align__(16) uint2 s_cell[kApplyCells][256];         // (p1, p2 | q1, q2) as 4 x fp16 (bytes are exact in fp16)
     __shared__ float2 s_ya[kApplyMaxBandRows];                        // (ya1, ya) of the CTA's rows
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -383,6 +386,7 @@ __global__ void __launch_bounds__(1024) clahe_apply_kernel(const uint8_t* __rest
 __global__ void __launch_bounds__(256) copy_image_kernel(const uint8_t* __restrict__ src, int src_pitch,
                                                          int64_t src_stride, uint8_t* __restrict__ dst,
                                                          int dst_pitch, int64_t dst_stride, int W, int H) {
+    pdl_entry();
     const int s = blockIdx.y;
     const int wq = (W + 3) >> 2;
     for (int idx = blockIdx.x * 256 + threadIdx.x; idx < wq * H; idx += gridDim.x * 256) {
@@ -422,7 +426,7 @@ static void launch_lut_nt2(const uint8_t* src, int src_pitch, int64_t src_stride
         cudaFuncSetAttribute(clahe_lut_kernel<NT, FULLW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = true;
     }
-    clahe_lut_kernel<NT, FULLW><<<dim3(kClaheTiles * kClaheTiles, n_streams), NT, smem, st>>>(
+    launch_pdl(clahe_lut_kernel<NT, FULLW>, dim3(kClaheTiles * kClaheTiles, n_streams), dim3(NT), smem, st,
         src, src_pitch, src_stride, g.tw, g.th, g.clip, g.lut_scale, luts);
 }
 template <int NT>
@@ -447,7 +451,7 @@ void launch_clahe_lut_only(const uint8_t* src, int src_pitch, int64_t src_stride
     else if (exact_tiles && 4 * ((words + 127) / 128) <= 255) launch_lut_nt<128>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else if (exact_tiles && 4 * ((words + 255) / 256) <= 255 && area < 65536) launch_lut_nt<256>(src, src_pitch, src_stride, g, n_streams, luts, st);
     else
-        clahe_lut_generic_kernel<<<dim3(kClaheTiles * kClaheTiles, n_streams), 256, 0, st>>>(
+        launch_pdl(clahe_lut_generic_kernel, dim3(kClaheTiles * kClaheTiles, n_streams), dim3(256), 0, st,
             src, src_pitch, src_stride, W, H, g.tw, g.th, g.clip, g.lut_scale, luts);
 }
 
@@ -470,7 +474,7 @@ void launch_clahe_apply_only(const uint8_t* src, int src_pitch, int64_t src_stri
     const int nchunks = (W + 255) / 256;
     int nwarps = nchunks < 32 ? nchunks : 32;
     if (nwarps < 8) nwarps = (8 / nchunks) * nchunks;          // row groups fill the CTA up to 8 warps
-    clahe_apply_kernel<<<dim3((kClaheTiles + 1) * kApplyRowSplit, n_streams), 32 * nwarps, 0, st>>>(
+    launch_pdl(clahe_apply_kernel, dim3((kClaheTiles + 1) * kApplyRowSplit, n_streams), dim3(32 * nwarps), 0, st,
         src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, inv_tw, inv_th, bands, luts);
 }
 
@@ -487,7 +491,7 @@ void launch_copy_image(const uint8_t* src, int src_pitch, int64_t src_stride, ui
     const int wq = (W + 3) >> 2;
     int blocks = (wq * H + 255) / 256;
     if (blocks > 1024) blocks = 1024;
-    copy_image_kernel<<<dim3(blocks, n_streams), 256, 0, st>>>(src, src_pitch, src_stride, dst, dst_pitch,
+    launch_pdl(copy_image_kernel, dim3(blocks, n_streams), dim3(256), 0, st, src, src_pitch, src_stride, dst, dst_pitch,
                                                                dst_stride, W, H);
     if (launches) *launches += 1;
 }

@@ -144,7 +144,8 @@ __device__ __forceinline__ void bitonic_sort_desc_u64(unsigned long long* v, int
     }
 }
 
-__global__ void __launch_bounds__(256) post_lk_kernel(GlueParams g) { post_lk_body(g, blockIdx.x, threadIdx.x); }
+__global__ void __launch_bounds__(256) post_lk_kernel(GlueParams g) {
+    pdl_entry(); post_lk_body(g, blockIdx.x, threadIdx.x); }
 
 __device__ __forceinline__ void set_mask_body(const GlueParams& g, const int s, const int tid, uint8_t* dsm) {
     unsigned long long* ck = reinterpret_cast<unsigned long long*>(dsm);   // (key, position) sort keys
@@ -462,6 +463,7 @@ __device__ __forceinline__ void set_mask_body(const GlueParams& g, const int s, 
 }
 
 __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
+    pdl_entry();
     extern __shared__ __align__(16) uint8_t dsm[];
     set_mask_body(g, blockIdx.x, threadIdx.x, dsm);
 }
@@ -469,6 +471,7 @@ __global__ void __launch_bounds__(256) set_mask_kernel(GlueParams g) {
 // post_lk + set_mask in one launch (no RANSAC stage between them): both are one CTA per stream, and a CTA only
 // consumes what it wrote itself, so a block barrier is all the ordering needed
 __global__ void __launch_bounds__(256) post_lk_set_mask_kernel(GlueParams g) {
+    pdl_entry();
     extern __shared__ __align__(16) uint8_t dsm[];
     post_lk_body(g, blockIdx.x, threadIdx.x);
     __syncthreads();
@@ -477,6 +480,7 @@ __global__ void __launch_bounds__(256) post_lk_set_mask_kernel(GlueParams g) {
 
 // ... and with the device F-matrix RANSAC between them (VS_RANSAC_DEVICE): still one CTA per stream end to end
 __global__ void __launch_bounds__(256) post_lk_ransac_set_mask_kernel(GlueParams g, unsigned int seed) {
+    pdl_entry();
     extern __shared__ __align__(16) uint8_t dsm[];
     static_assert(kRansacThreads == 256, "glue kernels run 256 threads per stream");
     post_lk_body(g, blockIdx.x, threadIdx.x);
@@ -556,6 +560,7 @@ __device__ __forceinline__ int greedy_accept(const unsigned long long* v, int nv
 }
 
 __global__ void __launch_bounds__(kFinishThreads) select_finish_kernel(GlueParams g) {
+    pdl_entry();
     extern __shared__ __align__(16) uint8_t dsm[];
     unsigned long long* skeys = reinterpret_cast<unsigned long long*>(dsm);       // [kSortSmemKeys]
     int* hist = reinterpret_cast<int*>(skeys + kSortSmemKeys);                     // [kSelBins]
@@ -729,6 +734,7 @@ __global__ void __launch_bounds__(kFinishThreads) select_finish_kernel(GlueParam
 }
 
 __global__ void undistort_kernel(CameraDev cam, const float2* __restrict__ pts, int n, float2* __restrict__ out) {
+    pdl_entry();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double X, Y, Z;
@@ -737,7 +743,7 @@ __global__ void undistort_kernel(CameraDev cam, const float2* __restrict__ pts, 
 }
 
 void launch_post_lk(const GlueParams& g, cudaStream_t st, int64_t* launches) {
-    post_lk_kernel<<<g.n_streams, 256, 0, st>>>(g);
+    launch_pdl(post_lk_kernel, dim3(g.n_streams), dim3(256), 0, st, g);
     if (launches) *launches += 1;
 }
 
@@ -752,9 +758,9 @@ void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bo
         cudaFuncSetAttribute(post_lk_ransac_set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    if (with_post_lk && with_ransac) post_lk_ransac_set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g, seed);
-    else if (with_post_lk) post_lk_set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
-    else set_mask_kernel<<<g.n_streams, 256, smem, st>>>(g);
+    if (with_post_lk && with_ransac) launch_pdl(post_lk_ransac_set_mask_kernel, dim3(g.n_streams), dim3(256), smem, st, g, seed);
+    else if (with_post_lk) launch_pdl(post_lk_set_mask_kernel, dim3(g.n_streams), dim3(256), smem, st, g);
+    else launch_pdl(set_mask_kernel, dim3(g.n_streams), dim3(256), smem, st, g);
     if (launches) *launches += 1;
 }
 
@@ -765,7 +771,7 @@ void launch_select_finish(const GlueParams& g, cudaStream_t st, int64_t* launche
         cudaFuncSetAttribute(select_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    select_finish_kernel<<<g.n_streams, kFinishThreads, smem, st>>>(g);
+    launch_pdl(select_finish_kernel, dim3(g.n_streams), dim3(kFinishThreads), smem, st, g);
     if (launches) *launches += 1;
 }
 

@@ -57,6 +57,7 @@ __device__ __forceinline__ void stage_tile(uint8_t* tile, int tpitch, int rows, 
 
 template <int WIN>
 __global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_kernel(LkParams p) {
+    pdl_entry();
     extern __shared__ __align__(16) uint8_t smem[];
     const int win = WIN ? WIN : p.win;
     constexpr int KMAX = WIN ? (WIN * WIN + 31) / 32 : (kMaxWin * kMaxWin + 31) / 32;
@@ -508,6 +509,7 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
 // launches: launch k drains counter k&1 and clears the other one for launch k+1 (stream order makes that safe).
 __global__ void __launch_bounds__(32 * kLkWarpsPerCta, 5) lk_fast21_kernel(LkParams p, int n_streams, int max_features,
                                                                         int* counters, int which) {
+    pdl_entry();
     __shared__ __align__(16) uint32_t s_tiles[kLkWarpsPerCta][kFastWarpSmem / 4];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (blockIdx.x == 0 && threadIdx.x == 0) counters[which ^ 1] = 0;
@@ -539,7 +541,7 @@ int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t s
             resident = sms * (per_sm > 0 ? per_sm : 1);
         }
         const int need = (n_streams * max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta;
-        lk_fast21_kernel<<<need < resident ? need : resident, 32 * kLkWarpsPerCta, 0, st>>>(p, n_streams, max_features,
+        launch_pdl(lk_fast21_kernel, dim3(need < resident ? need : resident), dim3(32 * kLkWarpsPerCta), 0, st, p, n_streams, max_features,
                                                                                           p.work_counters, p.work_seq & 1);
     } else {
         const int smem = kLkWarpsPerCta * lk_warp_smem(p.win);
@@ -549,7 +551,7 @@ int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t s
                                  kLkWarpsPerCta * lk_warp_smem(kMaxWin));
             attr_set = true;
         }
-        lk_kernel<0><<<grid, 32 * kLkWarpsPerCta, smem, st>>>(p);
+        launch_pdl(lk_kernel<0>, grid, dim3(32 * kLkWarpsPerCta), smem, st, p);
     }
     if (launches) *launches += 1;
     return 0;

@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(32 * kPdWarps) pyr_down_kernel(const uint8_t* 
                                                                  int spitch, uint8_t* __restrict__ dst, int dw, int dh,
                                                                  int dpitch, int64_t stream_stride, int nx, int ny,
                                                                  int groups_per_strip, int rows_per_strip) {
+    pdl_entry();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int strip = blockIdx.x * kPdWarps + warp;
     if (strip >= nx * ny) return;
@@ -144,7 +145,7 @@ void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from,
     const int rows = b.h >= 192 ? 16 : 8;
     const int ny = (b.h + rows - 1) / rows;
     dim3 grid((nx * ny + kPdWarps - 1) / kPdWarps, n_streams);
-    pyr_down_kernel<<<grid, 32 * kPdWarps, 0, st>>>(pyr_base + a.offset, a.w, a.h, a.pitch,
+    launch_pdl(pyr_down_kernel, grid, dim3(32 * kPdWarps), 0, st, pyr_base + a.offset, a.w, a.h, a.pitch,
                                                     const_cast<uint8_t*>(pyr_base) + b.offset, b.w, b.h, b.pitch,
                                                     pd.stream_bytes, nx, ny, gps, rows);
     if (launches) *launches += 1;

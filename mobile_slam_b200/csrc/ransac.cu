@@ -5,6 +5,7 @@
 namespace vs {
 
 __global__ void __launch_bounds__(kRansacThreads) ransac_kernel(GlueParams g, unsigned int seed) {
+    pdl_entry();
     extern __shared__ __align__(16) uint8_t dsm[];
     ransac_body(g, seed, blockIdx.x, threadIdx.x, dsm);
 }
@@ -18,7 +19,7 @@ int launch_ransac(vs_tracker* t) {
         cudaFuncSetAttribute(ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    ransac_kernel<<<t->B, kRansacThreads, smem, t->stream>>>(t->g, (unsigned)(t->lk_seq * 2654435761u + 12345u) /* = ransac_seed() in tracker.cu */);
+    launch_pdl(ransac_kernel, dim3(t->B), dim3(kRansacThreads), smem, t->stream, t->g, (unsigned)(t->lk_seq * 2654435761u + 12345u) /* = ransac_seed() in tracker.cu */);
     t->launches += 1;
     return VS_OK;
 }

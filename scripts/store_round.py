@@ -9,7 +9,8 @@ unit = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1}
 traffic = {"workload": f"C2 752x480, {streams} streams per launch, steady state (bench.py --steps 3 --warmup 3)",
            "source": f"ncu --set full --clock-control none, profiles/{tag}_ncu_<kernel>.txt: dram__bytes_read.sum + dram__bytes_write.sum per launch",
            "streams": streams, "kernels": {}}
-for k, name in [("lk_fast21", "lk"), ("shi_tomasi", "shi_tomasi"), ("clahe_lut", "clahe_lut"), ("clahe_apply", "clahe_apply"), ("pyr_down", "pyr_down")]:
+for k, name in [("lk_fast21", "lk"), ("shi_tomasi", "shi_tomasi"), ("clahe_lut", "clahe_lut"), ("clahe_apply", "clahe_apply"), ("pyr_down", "pyr_down"),
+                ("post_lk_ransac_set_mask", "post_lk_ransac_set_mask"), ("select_finish", "select_finish")]:
     rep = os.path.join(go, f"{tag}_{k}_kernel.ncu-rep")
     if not os.path.exists(rep):
         continue
@@ -21,6 +22,9 @@ for k, name in [("lk_fast21", "lk"), ("shi_tomasi", "shi_tomasi"), ("clahe_lut",
     b = float(r.group(2)) * unit[r.group(1)] + float(w.group(2)) * unit[w.group(1)]
     traffic["kernels"][name] = {"dram_bytes_per_launch": b, "dram_bytes_per_stream": b / streams, "ncu_duration_" + d.group(1): float(d.group(2))}
 json.dump(traffic, open(os.path.join(pr, f"{tag}_traffic.json"), "w"), indent=1)
+lat = os.path.join(go, f"{tag}_latency.txt")
+if os.path.exists(lat):
+    open(os.path.join(pr, f"{tag}_latency.txt"), "w").write(open(lat).read())
 src = os.path.join(go, f"{tag}_launches.csv")
 if os.path.exists(src):
     open(os.path.join(pr, f"{tag}_launches.csv"), "w").write(open(src).read())

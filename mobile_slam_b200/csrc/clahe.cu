@@ -405,8 +405,11 @@ struct ClaheGeom {
     float lut_scale;
 };
 static ClaheGeom clahe_geom(int W, int H) {
-    const int We = (W + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
-    const int He = (H + kClaheTiles - 1) / kClaheTiles * kClaheTiles;
+    // cv::CLAHE::apply pads right / bottom by tiles - (size % tiles) as soon as EITHER side is not a multiple of the
+    // tile grid, so a side that already is a multiple grows by a full 8 (checked against cv2 4.13: 120 x 90 -> 128 x 96)
+    const bool pad = (W % kClaheTiles) != 0 || (H % kClaheTiles) != 0;
+    const int We = pad ? W + kClaheTiles - W % kClaheTiles : W;
+    const int He = pad ? H + kClaheTiles - H % kClaheTiles : H;
     ClaheGeom g;
     g.tw = We / kClaheTiles;
     g.th = He / kClaheTiles;

@@ -166,13 +166,21 @@ class BatchTracker:
         """frames: sequence of n_streams (H, W) uint8 host arrays; times: n_streams floats."""
         if len(frames) != self.n_streams:
             raise ValueError("one frame per stream expected")
-        fr = [np.ascontiguousarray(f, np.uint8) for f in frames]
+        # row-strided views (a cv::Mat with step > cols, vio_engine.cpp:180 wraps the caller's buffer without a copy)
+        # go to the library as they are; anything else is made contiguous first
+        steps = {f.strides[0] for f in frames
+                 if isinstance(f, np.ndarray) and f.dtype == np.uint8 and f.ndim == 2 and f.strides[1] == 1}
+        if len(steps) == 1 and all(isinstance(f, np.ndarray) and f.dtype == np.uint8 and f.ndim == 2
+                                   and f.strides[1] == 1 for f in frames):
+            fr, stride = list(frames), steps.pop()
+        else:
+            fr, stride = [np.ascontiguousarray(f, np.uint8) for f in frames], self.tc.col
         for f in fr:
             if f.shape != (self.tc.row, self.tc.col):
                 raise ValueError(f"frame shape {f.shape} != {(self.tc.row, self.tc.col)}")
         ptrs = (C.c_void_p * self.n_streams)(*[f.ctypes.data for f in fr])
         ts = (C.c_double * self.n_streams)(*[float(t) for t in times])
-        _abi.check(self._lib.vs_tracker_track_batch(self._h, ptrs, self.tc.col, ts, self._res))
+        _abi.check(self._lib.vs_tracker_track_batch(self._h, ptrs, stride, ts, self._res))
         return self._collect() if collect else None
 
     def track_pinned(self, base_ptr: int, image_stride: int, times_ctypes, collect: bool = False):

@@ -31,7 +31,9 @@ def clahe_lut(src: np.ndarray, clip_limit: float = 3.0, tiles: int = 8):
     """Per-tile LUTs, shape (tiles*tiles, 256) uint8, and the (possibly padded) source."""
     h, w = src.shape
     if h % tiles or w % tiles:
-        ph, pw = (tiles - h % tiles) % tiles, (tiles - w % tiles) % tiles
+        # cv::CLAHE pads BOTH sides by tiles - (size % tiles) as soon as either one is not a multiple: a dimension that
+        # already is a multiple gets a full extra `tiles` rows / columns (verified against cv2 4.13, e.g. 120 x 90)
+        ph, pw = tiles - h % tiles, tiles - w % tiles
         ys = reflect101(np.arange(h + ph), h)
         xs = reflect101(np.arange(w + pw), w)
         src_e = src[np.ix_(ys, xs)]

@@ -124,8 +124,25 @@ def camera():
     np.savez_compressed(os.path.join(OUT, "camera.npz"), **out, **{f"meta_{k}": v for k, v in META.items()})
 
 
+CLAHE_PAD_SHAPES = [(120, 90), (104, 100), (90, 120), (97, 96)]     # (W, H): one or both sides off the 8 x 8 tile grid
+
+
+def clahe_padding():
+    """cv::CLAHE on shapes that need its padding rule (a side that is a multiple of 8 still grows by 8)."""
+    out = {}
+    for w, h in CLAHE_PAD_SHAPES:
+        img = cv2.GaussianBlur(np.random.default_rng(w * 1000 + h).integers(0, 256, (h, w), dtype=np.uint8), (0, 0), 2.0)
+        out[f"in_{w}x{h}"] = img
+        out[f"out_{w}x{h}"] = cv2.createCLAHE(3.0, (8, 8)).apply(img)
+    np.savez_compressed(os.path.join(OUT, "clahe_padding.npz"), **out, **{f"meta_{k}": v for k, v in META.items()})
+
+
 if __name__ == "__main__":
+    if "--only-clahe-padding" in sys.argv:
+        clahe_padding()
+        raise SystemExit(0)
     stages()
+    clahe_padding()
     sequence("sequence_small.npz", SEQ_CFG, 7, 8)
     sequence("sequence_fisheye.npz", SEQ_FISH_CFG, 9, 6)
     camera()

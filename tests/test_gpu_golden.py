@@ -45,6 +45,19 @@ def test_clahe_golden(small, g):
     assert np.array_equal(small.stage_clahe(g["frame1"]), g["clahe1"])
 
 
+def test_clahe_padding_golden(built_lib):
+    # cv::CLAHE's padding rule (a side on the 8 x 8 tile grid still grows by 8 when the other side is off it)
+    c = np.load(os.path.join(GOLD, "clahe_padding.npz"))
+    for k in [k for k in c.files if k.startswith("in_")]:
+        img, ref = c[k], c["out_" + k[3:]]
+        h, w = img.shape
+        tc = TrackerConfig(col=w, row=h, max_cnt=40, min_dist=10, ransac_mode=VS_RANSAC_OFF, capacity=256)
+        t = BatchTracker(tc, CameraParams(width=w, height=h, cx=w / 2, cy=h / 2), 1)
+        got = t.stage_clahe(img)
+        t.close()
+        assert np.array_equal(got, ref), (k, int(np.count_nonzero(got != ref)))
+
+
 def test_pyramid_golden(small, g):
     lv = small.stage_pyramid(g["clahe0"])
     assert len(lv) == int(g["n_levels"])

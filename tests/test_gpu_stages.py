@@ -55,6 +55,21 @@ def test_clahe_bit_exact(trackers, name):
     assert np.array_equal(got, ref), f"{np.count_nonzero(got != ref)} pixels differ"
 
 
+@pytest.mark.parametrize("shape", [(120, 90), (128, 90), (104, 100), (200, 90), (120, 180), (752, 90), (97, 96), (90, 120)])
+def test_clahe_padding_rule(built_lib, shape):
+    # one side a multiple of the 8 x 8 tile grid, the other not: cv::CLAHE pads BOTH (the aligned side by a full 8)
+    w, h = shape
+    cfg = dict(ODD, width=w, height=h, intr=(100.0, 100.0, w / 2.0, h / 2.0))
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    bt = BatchTracker(tc, cam, 1)
+    img = cv2.GaussianBlur(np.random.default_rng(w * 1000 + h).integers(0, 256, (h, w), dtype=np.uint8), (0, 0), 2.0)
+    ref = cv2.createCLAHE(3.0, (8, 8)).apply(img)
+    got = bt.stage_clahe(img)
+    bt.close()
+    assert np.array_equal(got, ref), f"{np.count_nonzero(got != ref)} pixels differ"
+    assert np.array_equal(spec.clahe(img), ref)
+
+
 def test_clahe_extremes(trackers):
     t = trackers("C1")
     for img in (np.zeros((512, 512), np.uint8), np.full((512, 512), 255, np.uint8),

@@ -26,6 +26,15 @@ def test_clahe_bit_exact_vs_golden(g):
     assert np.array_equal(spec.clahe(g["frame1"]), g["clahe1"])
 
 
+def test_clahe_padding_rule_vs_golden():
+    # shapes where cv::CLAHE pads: one or both sides off the 8 x 8 tile grid (a side on the grid still grows by 8)
+    c = np.load(os.path.join(GOLD, "clahe_padding.npz"))
+    shapes = [k[3:] for k in c.files if k.startswith("in_")]
+    assert len(shapes) >= 4
+    for sh in shapes:
+        assert np.array_equal(spec.clahe(c["in_" + sh]), c["out_" + sh]), sh
+
+
 def test_pyramid_and_scharr_bit_exact_vs_golden(g):
     levels = spec.build_pyramid(g["clahe0"], 21, 3)
     assert len(levels) == int(g["n_levels"])
@@ -145,6 +154,16 @@ def test_clahe_pyramid_live(shape):
     for l in range(len(lv)):
         assert np.array_equal(lv[l], pyr[2 * l])
         assert np.array_equal(spec.scharr_deriv(lv[l]), pyr[2 * l + 1])
+
+
+@pytest.mark.parametrize("shape", [(120, 90), (128, 90), (104, 100), (200, 90), (120, 180), (90, 120), (97, 96), (120, 96)])
+def test_clahe_padding_rule_live(shape):
+    # cv::CLAHE pads by tiles - (size % tiles) on BOTH sides as soon as either one is not a multiple of 8: a side that
+    # already is a multiple still grows by 8 (120 x 90 is equalised as 128 x 96)
+    cv2 = _cv2()
+    w, h = shape
+    img = cv2.GaussianBlur(np.random.default_rng(w * 1000 + h).integers(0, 256, (h, w), dtype=np.uint8), (0, 0), 2.0)
+    assert np.array_equal(spec.clahe(img), cv2.createCLAHE(3.0, (8, 8)).apply(img))
 
 
 def test_gftt_live():

@@ -19,7 +19,7 @@ int launch_ransac(vs_tracker* t) {
         cudaFuncSetAttribute(ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    launch_pdl(ransac_kernel, dim3(t->B), dim3(kRansacThreads), smem, t->stream, t->g, (unsigned)(t->lk_seq * 2654435761u + 12345u) /* = ransac_seed() in tracker.cu */);
+    launch_pdl(ransac_kernel, dim3(t->B), dim3(kRansacThreads), smem, t->stream, t->g, 12345u /* = ransac_seed() in tracker.cu */);
     t->launches += 1;
     return VS_OK;
 }
@@ -49,7 +49,7 @@ extern "C" int vs_stage_ransac(vs_tracker* t, const float* a_xy, const float* b_
         cudaFuncSetAttribute(ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         configured = smem;
     }
-    ransac_kernel<<<1, kRansacThreads, smem, t->stream>>>(g1, 777u);
+    ransac_kernel<<<1, kRansacThreads, smem, t->stream>>>(g1, 12345u);
     t->launches += 1;
     VS_CUDA_TRY(cudaMemcpyAsync(status, g.w_rstatus, (size_t)n, cudaMemcpyDeviceToHost, t->stream));
     VS_CUDA_TRY(cudaMemsetAsync(g.n, 0, sizeof(int) * t->B, t->stream));

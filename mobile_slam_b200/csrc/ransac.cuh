@@ -292,13 +292,17 @@ __device__ __forceinline__ void ransac_body(const GlueParams& g, const unsigned 
     nb.s = d2 > 1e-12 ? 1.4142135623730951 / d2 : 1.0;
 
     const float thr2 = (float)(g.f_threshold * g.f_threshold);
+    // The sample sequence is seeded from the stream's own points, not from its position in a batch, a lane or a GPU:
+    // a stream's mask is the same wherever and with whatever neighbours it is tracked (`seed` only salts it).
+    const unsigned seed0 = hash32((unsigned)n * 0x9E3779B1u ^ __float_as_uint(pa[0].x) ^ hash32(__float_as_uint(pb[0].y)) ^
+                                  hash32(__float_as_uint(pa[n - 1].y) + 0x85ebca6bu) ^ hash32(__float_as_uint(pb[n >> 1].x) + seed));
     const int j = lane & (kRansacGroup - 1), gbase = lane & ~(kRansacGroup - 1), grp = lane / kRansacGroup;
     const int slot0 = warp * kRansacSlotsPerWarp;
     unsigned long long wbest = 0ull, best = 0ull;         // warp's / CTA's best (inliers << 32 | ~model id)
     int need = kRansacMaxIters, done = 0, par = 0;
     while (done < need) {
         const int h = done + warp * (32 / kRansacGroup) + grp;
-        unsigned st = hash32(seed ^ hash32((unsigned)s * 0x9E3779B1u + (unsigned)h));
+        unsigned st = hash32(seed0 + (unsigned)h * 0x9E3779B1u);
         int idx[7];
 #pragma unroll
         for (int k = 0; k < 7; ++k) {

@@ -482,7 +482,9 @@ void vs_tracker_destroy(vs_tracker* t) {
 namespace vs {
 
 int launch_ransac(vs_tracker* t);   // ransac.cu
-static inline unsigned ransac_seed(const vs_tracker* t) { return (unsigned)(t->lk_seq * 2654435761u + 12345u); }
+// constant salt: the per-stream seed comes from the stream's points (ransac.cuh), so results do not depend on
+// how streams are batched, split into lanes or spread over handles
+static inline unsigned ransac_seed(const vs_tracker*) { return 12345u; }
 
 static void fill_lk_params(vs_tracker* t, LkParams& p, int prev_buf, int next_buf, const float2* pts, float2* out,
                            uint8_t* status) {

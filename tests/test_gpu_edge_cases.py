@@ -117,3 +117,102 @@ def test_tiny_frame_fewer_pyramid_levels(built_lib):
     out = _run_both(cfg, frames, [0.05 * k for k in range(5)])
     assert len(out[0][0].ids) > 5
     _assert_same(out)
+
+
+def test_runtime_mutators_match_reference_config_changes(built_lib):
+    # VIOEngine::setMobileParams / setTrackingParams rewrite g_config between frames (vio_engine.cpp:354-389); the
+    # handle's vs_tracker_set_params must have the same effect on the very next frame
+    cfg = CONFIGS["C2"]
+    st = SynthStream(23, cfg["width"], cfg["height"], motion=1.5)
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, capacity=512)
+    bt = BatchTracker(tc, cam, 1)
+    ref = R.RefFeatureTracker(R.config_from_synth(cfg, use_ransac=False), ocam.from_config(cfg))
+    changes = {3: dict(max_cnt=200, min_dist=20), 5: dict(lk_window=15, lk_pyramid=2, lk_iterations=20, lk_eps=0.03),
+               7: dict(max_cnt=100, min_dist=35), 9: dict(lk_window=31, lk_pyramid=4)}
+    names = dict(max_cnt="max_cnt", min_dist="min_dist", lk_window="lk_window_size", lk_pyramid="lk_pyramid_levels",
+                 lk_iterations="lk_iterations", lk_eps="lk_eps")
+    exact = 0
+    for k in range(12):
+        if k in changes:
+            bt.set_params(**changes[k])
+            for a, v in changes[k].items():
+                setattr(ref.cfg, names[a], v)
+        f = st.frame(k)
+        r = bt.track([f], [0.05 * k])[0]
+        ref.detect_and_track(f, 0.05 * k)
+        ref.update_all_ids()
+        same = r.ids.tolist() == list(ref.ids) and r.track_cnt.tolist() == list(ref.track_cnt)
+        exact += same
+        if same:
+            assert np.abs(r.cur_pts - np.array(ref.cur_pts, np.float32).reshape(-1, 2)).max() <= 0.01, k
+        if k == 4:
+            assert 150 < len(r.ids) <= 200
+    assert exact >= 11, f"{exact}/12 frames identical"
+    bt.close()
+
+
+def test_callback_ransac_on_a_multi_lane_batch(built_lib):
+    # the host hop of VS_RANSAC_CALLBACK with several streams split over pipeline lanes: each stream's callback sees
+    # its own points, and the batch equals the same streams tracked one handle each
+    from mobile_slam_b200 import VS_RANSAC_CALLBACK
+    cfg = dict(CONFIGS["C2"])
+    S = 4
+    streams = [SynthStream(500 + s, cfg["width"], cfg["height"], motion=2.0) for s in range(S)]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_CALLBACK)
+    tcl, _ = config_from_synth(cfg, ransac_mode=VS_RANSAC_CALLBACK, pipeline_lanes=2)
+    seen = {"batch": set(), "single": 0}
+
+    def make(tag):
+        def reject(stream, a, b, px):
+            if tag == "batch":
+                seen["batch"].add(stream)
+            else:
+                seen["single"] += 1
+            _, status = cv2.findFundamentalMat(a, b, cv2.FM_RANSAC, 1.0, 0.99)
+            return np.ones(len(a), np.uint8) if status is None else status.reshape(-1)
+        return reject
+    batch = BatchTracker(tcl, cam, S)
+    batch.set_reject_callback(make("batch"))
+    singles = [BatchTracker(tc, cam, 1) for _ in range(S)]
+    for t in singles:
+        t.set_reject_callback(make("single"))
+    for k in range(6):
+        frames = [st.frame(k) for st in streams]
+        rb = batch.track(frames, [0.05 * k] * S)
+        for s in range(S):
+            r1 = singles[s].track([frames[s]], [0.05 * k])[0]
+            assert rb[s].ids.tolist() == r1.ids.tolist() and rb[s].track_cnt.tolist() == r1.track_cnt.tolist(), (k, s)
+            assert np.array_equal(rb[s].cur_pts, r1.cur_pts)
+    assert seen["batch"] == set(range(S)) and seen["single"] > 0
+    batch.close()
+    for t in singles:
+        t.close()
+
+
+def test_device_ransac_and_fb_check_through_submit_wait_and_lanes(built_lib):
+    # the asynchronous pair and the lane split must not change what the device RANSAC (per-frame seed) and the
+    # forward/backward check produce
+    from mobile_slam_b200 import VS_RANSAC_DEVICE
+    cfg = CONFIGS["C1"]
+    S = 4
+    streams = [SynthStream(700 + s, cfg["width"], cfg["height"], motion=2.0) for s in range(S)]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_DEVICE, fb_check=1)
+    tcl, _ = config_from_synth(cfg, ransac_mode=VS_RANSAC_DEVICE, fb_check=1, pipeline_lanes=2)
+    sync, asyn = BatchTracker(tc, cam, S), BatchTracker(tcl, cam, S)
+    frames = [[st.frame(k) for st in streams] for k in range(8)]
+    got = []
+    asyn.submit(frames[0], [0.0] * S)
+    for k in range(1, 8):
+        asyn.submit(frames[k], [0.05 * k] * S)
+        got.append(asyn.wait())
+    got.append(asyn.wait())
+    ran = 0
+    for k in range(8):
+        rs = sync.track(frames[k], [0.05 * k] * S)
+        for s in range(S):
+            assert rs[s].ids.tolist() == got[k][s].ids.tolist() and rs[s].track_cnt.tolist() == got[k][s].track_cnt.tolist(), (k, s)
+            assert np.array_equal(rs[s].cur_pts, got[k][s].cur_pts) and np.array_equal(rs[s].pts_velocity, got[k][s].pts_velocity)
+            ran += rs[s].counters["ransac_ran"]
+    assert ran >= 12
+    sync.close()
+    asyn.close()

@@ -11,7 +11,7 @@ C5 (64 independent 512x512 streams) and C4 (1280x720, 2000 features).  What must
 import numpy as np
 import pytest
 
-from mobile_slam_b200 import BatchTracker, VS_RANSAC_OFF, config_from_synth
+from mobile_slam_b200 import BatchTracker, VS_RANSAC_DEVICE, VS_RANSAC_OFF, config_from_synth
 from mobile_slam_b200.synth import CONFIGS, SynthStream
 
 pytestmark = pytest.mark.gpu
@@ -73,13 +73,16 @@ def _check_frame(cfg, prev, cur, k):
     assert np.all(np.isfinite(cur.cur_undistorted_pts)) and np.all(np.isfinite(cur.pts_velocity))
 
 
-def test_c5_64_streams_invariants_and_independence(built_lib):
+@pytest.mark.parametrize("mode", [VS_RANSAC_OFF, VS_RANSAC_DEVICE], ids=["ransac_off", "ransac_device"])
+def test_c5_64_streams_invariants_and_independence(built_lib, mode):
+    # with the device F-matrix RANSAC too: its sample sequence is seeded from the stream's own points, so a stream's
+    # result does not depend on where it sits in a batch, a lane or a handle
     cfg = CONFIGS["C1"]
     S, F = 64, 8
     streams = [SynthStream(700 + s, cfg["width"], cfg["height"], motion=1.0 + (s % 4)) for s in range(S)]
     frames = [np.stack([st.frame(k) for st in streams]) for k in range(F)]
-    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
-    tc8, _ = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, pipeline_lanes=8)
+    tc, cam = config_from_synth(cfg, ransac_mode=mode)
+    tc8, _ = config_from_synth(cfg, ransac_mode=mode, pipeline_lanes=8)
     whole, lanes = BatchTracker(tc, cam, S), BatchTracker(tc8, cam, S)
     halves = [BatchTracker(tc, cam, S // 2), BatchTracker(tc, cam, S // 2)]     # "2 GPUs": streams s mod 2
     prev = [None] * S
@@ -100,11 +103,12 @@ def test_c5_64_streams_invariants_and_independence(built_lib):
         t.close()
 
 
-def test_c4_2000_features_invariants_and_determinism(built_lib):
+@pytest.mark.parametrize("mode", [VS_RANSAC_OFF, VS_RANSAC_DEVICE], ids=["ransac_off", "ransac_device"])
+def test_c4_2000_features_invariants_and_determinism(built_lib, mode):
     cfg = CONFIGS["C4"]
     st = SynthStream(900, cfg["width"], cfg["height"], motion=2.0)
     frames = [st.frame(k) for k in range(5)]
-    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    tc, cam = config_from_synth(cfg, ransac_mode=mode)
     runs = []
     for rep in range(2):
         bt = BatchTracker(tc, cam, 1)

@@ -12,7 +12,7 @@
 //                             feature_tracker.cpp:203-307 runs through cv::findFundamentalMat (VS_RANSAC_CALLBACK),
 //                             i.e. bit-for-bit the reference's own call.
 //   (default, no OpenCV)      vs::Point2f / vs::ImageView stand-ins with the same field names (x, y / data, cols, rows,
-//                             step); rejection = VS_RANSAC_OFF or VS_RANSAC_DEVICE as configured.
+//                             step); rejection = the built-in device RANSAC (VS_RANSAC_DEVICE, default) or VS_RANSAC_OFF as configured.
 //   -DVS_WITH_REFERENCE_CONFIG  read utility::g_config (include/utility/config.h:18-56) on every call like the
 //                             reference does; otherwise use the `config` member.
 #ifndef VS_FEATURE_TRACKER_HPP_
@@ -72,7 +72,7 @@ struct FrontendConfig {
 #ifdef VS_WITH_OPENCV
     int ransac_mode = VS_RANSAC_CALLBACK;
 #else
-    int ransac_mode = VS_RANSAC_OFF;
+    int ransac_mode = VS_RANSAC_DEVICE;   // the reference always rejects outliers; without OpenCV the built-in device RANSAC does
 #endif
 };
 

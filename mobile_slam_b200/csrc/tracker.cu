@@ -708,7 +708,8 @@ static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride,
                          const double* time_s, int slot = 0) {
     double* h_time = t->h_time + (size_t)slot * t->B;
     memcpy(h_time, time_s, sizeof(double) * t->B);
-    tl_pdl_launch = t->B <= kPdlMaxStreams;       // programmatic dependent launches for latency-sized handles only
+    static const int pdl_max = [] { const char* e = getenv("VS_PDL_MAX_STREAMS"); return e ? atoi(e) : kPdlMaxStreams; }();
+    tl_pdl_launch = t->B <= pdl_max;              // programmatic dependent launches for latency-sized handles only
     VS_CUDA_TRY(cudaEventRecord(t->ev0, t->stream));
     prof_begin(t);
     t->g.cur_time = h_time;      // pinned host memory is device-addressable (UVA): select_finish reads the B doubles in place

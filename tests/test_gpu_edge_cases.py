@@ -216,3 +216,38 @@ def test_device_ransac_and_fb_check_through_submit_wait_and_lanes(built_lib):
     assert ran >= 12
     sync.close()
     asyn.close()
+
+
+def test_fisheye_mask_image_with_grey_levels(built_lib):
+    # feature_tracker.cpp:42-46: a mask image replaces the generated circle.  setMask keeps a tracked point only where
+    # the mask is exactly 255 (:80), goodFeaturesToTrack detects wherever it is non-zero: a grey (1..254) region
+    # therefore gets new corners every frame and loses them again on the next one
+    cfg = dict(CONFIGS["C1"])
+    W, H = cfg["width"], cfg["height"]
+    m = np.full((H, W), 255, np.uint8)
+    m[:, :80] = 0                       # nothing on the left
+    m[:120, :] = 100                    # grey band on top
+    m[300:360, 200:420] = 0             # a hole
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, fisheye_mask=m)
+    bt = BatchTracker(tc, cam, 1)
+    ref = R.RefFeatureTracker(R.config_from_synth(cfg, use_ransac=False), ocam.from_config(cfg))
+    ref.fisheye_mask = m.copy()
+    st = SynthStream(61, W, H)
+    exact, grey_new = 0, 0
+    for k in range(8):
+        f = st.frame(k)
+        r = bt.track([f], [0.05 * k])[0]
+        ref.detect_and_track(f, 0.05 * k)
+        ref.update_all_ids()
+        same = r.ids.tolist() == list(ref.ids) and r.track_cnt.tolist() == list(ref.track_cnt)
+        exact += same
+        if same and len(r.ids):
+            assert np.abs(r.cur_pts - np.array(ref.cur_pts, np.float32).reshape(-1, 2)).max() <= 0.01, k
+        x, y = np.rint(r.cur_pts[:, 0]).astype(int), np.rint(r.cur_pts[:, 1]).astype(int)
+        assert np.all(m[y, x] != 0), k
+        old = r.track_cnt > 1
+        assert np.all(m[y[old], x[old]] == 255), k                      # survivors sit on 255 only
+        grey_new += int(np.sum(m[y[~old], x[~old]] == 100))
+    assert exact >= 7, exact
+    assert grey_new > 0
+    bt.close()

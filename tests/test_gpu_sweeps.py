@@ -23,3 +23,16 @@ def test_param_sweep(built_lib):
     from param_sweep import param_sweep
     bad = param_sweep(verbose=False)
     assert not bad, bad
+
+
+@pytest.mark.parametrize("name,motion,frames", [("C1", 1.0, 300), ("C2", 3.0, 300), ("C3", 2.0, 120)])
+def test_long_free_running_sequences(built_lib, name, motion, frames):
+    # 300 frames = the length of the reference's own trajectory parity test (tests/test_vio_engine_parity.cpp:305); C2 runs
+    # with 3x motion (EuRoC's frame_skip 2).  A free-running pair may renumber features after one
+    # borderline cvRound / status flip (1e-4 px LK differences), so ids are compared up to the first divergence and
+    # image positions over the whole run.
+    from long_sequence import long_sequence
+    r = long_sequence(name, motion, frames, verbose=False)
+    assert r["first_divergence"] is None or r["first_divergence"] >= 60, r
+    assert r["max_dpos_before_divergence"] <= 0.011, r
+    assert r["pos_match_frac"] >= 0.97, r

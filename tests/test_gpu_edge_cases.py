@@ -251,3 +251,40 @@ def test_fisheye_mask_image_with_grey_levels(built_lib):
     assert exact >= 7, exact
     assert grey_new > 0
     bt.close()
+
+
+def test_device_ransac_edge_recovery(built_lib):
+    # feature_tracker.cpp:236-285: with f_threshold_edge_factor > 0 a point rejected by the RANSAC mask is restored when
+    # it lies in the outer image region (r_ratio >= 0.3) and within F_threshold * (1 + factor * r_ratio^2) of its
+    # epipolar line.  Same stream through two handles (factor 0 and 3): while both still hold the same features the
+    # second one keeps a superset, and what it restores lies in the outer region.
+    from mobile_slam_b200 import VS_RANSAC_DEVICE
+    cfg = CONFIGS["C1"]
+    W, H = cfg["width"], cfg["height"]
+    st = SynthStream(77, W, H, motion=2.0)
+    tc0, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_DEVICE)
+    tc3, _ = config_from_synth(cfg, ransac_mode=VS_RANSAC_DEVICE, f_threshold_edge_factor=3.0)
+    a, b = BatchTracker(tc0, cam, 1), BatchTracker(tc3, cam, 1)
+    prev_same, restored, compared = True, 0, 0
+    r_max = np.hypot(W / 2.0, H / 2.0)
+    for k in range(40):
+        f = st.frame(k)
+        ra, rb = a.track([f], [0.05 * k])[0], b.track([f], [0.05 * k])[0]
+        if prev_same and ra.counters["ransac_ran"]:
+            assert rb.counters["ransac_ran"]
+            compared += 1
+            assert rb.counters["n_ransac_in"] == ra.counters["n_ransac_in"]
+            assert rb.counters["n_ransac_out"] >= ra.counters["n_ransac_out"], k
+            old_a = set(ra.ids[ra.track_cnt > 1].tolist())
+            extra = [i for i, c in zip(rb.ids.tolist(), rb.track_cnt.tolist()) if c > 1 and i not in old_a]
+            for i in extra:
+                p = rb.cur_pts[rb.ids.tolist().index(i)]
+                assert np.hypot(p[0] - W / 2.0, p[1] - H / 2.0) / r_max >= 0.3 - 1e-6, (k, i, p)
+            restored += rb.counters["n_ransac_out"] - ra.counters["n_ransac_out"]
+        prev_same = prev_same and ra.ids.tolist() == rb.ids.tolist()
+        if not prev_same:
+            break
+    assert compared >= 1
+    assert restored >= 1, "edge recovery never restored a point on this sequence"
+    a.close()
+    b.close()

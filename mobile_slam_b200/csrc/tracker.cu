@@ -132,6 +132,23 @@ static void sync_glue_params(vs_tracker* t) {
 }
 
 
+// results block: hdr | ids | cnt | pts | un | vel, in device memory (d_rblock, copied out after the frame) or — for
+// latency-sized handles — directly in a pinned host slot (the kernels' few KB of result stores go over PCIe as posted
+// writes, which saves the separate D2H copy and its DMA latency at the end of every frame)
+constexpr int kDirectResultsMaxStreams = 16;
+static void point_results(vs_tracker* t, uint8_t* base) {
+    GlueParams& g = t->g;
+    const int64_t B = t->B, C = t->cap;
+    uint8_t* p = base;
+    g.r_hdr = reinterpret_cast<int*>(p); p += B * kHdrInts * 4;
+    g.r_ids = reinterpret_cast<int*>(p); p += B * C * 4;
+    g.r_cnt = reinterpret_cast<int*>(p); p += B * C * 4;
+    g.r_pts = reinterpret_cast<float2*>(p); p += B * C * 8;
+    g.r_un = reinterpret_cast<float2*>(p); p += B * C * 8;
+    g.r_vel = reinterpret_cast<float2*>(p);
+}
+static inline bool direct_results(const vs_tracker* t) { return t->B <= kDirectResultsMaxStreams; }
+
 // ---- per-kernel CUDA-event profile (vs_tracker_set_profiling) ----
 static const char* const kProfNames[PK_COUNT] = {
     "input_copy", "clahe_lut", "clahe_apply", "pyr_down", "lk", "lk_backward", "post_lk", "ransac",
@@ -381,15 +398,7 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     // results block: hdr | ids | cnt | pts | un | vel
     t->h_block_bytes = (size_t)(B * kHdrInts * 4 + B * C * (4 + 4 + 8 + 8 + 8));
     VS_TRY_CREATE(A.alloc(&t->d_rblock, t->h_block_bytes));
-    {
-        uint8_t* p = t->d_rblock;
-        g.r_hdr = reinterpret_cast<int*>(p); p += B * kHdrInts * 4;
-        g.r_ids = reinterpret_cast<int*>(p); p += B * C * 4;
-        g.r_cnt = reinterpret_cast<int*>(p); p += B * C * 4;
-        g.r_pts = reinterpret_cast<float2*>(p); p += B * C * 8;
-        g.r_un = reinterpret_cast<float2*>(p); p += B * C * 8;
-        g.r_vel = reinterpret_cast<float2*>(p);
-    }
+    point_results(t, t->d_rblock);
     VS_TRY_CREATE(cudaMallocHost(&t->h_block, 2 * t->h_block_bytes));      // two result slots (submit / wait pipelining)
     memset(t->h_block, 0, 2 * t->h_block_bytes);
     VS_TRY_CREATE(cudaMallocHost(&t->h_time, 2 * sizeof(double) * B));
@@ -725,7 +734,9 @@ static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride,
         istride = t->raw_stride;
     }
     prof_tick(t, PK_INPUT);
+    if (direct_results(t)) point_results(t, t->h_block + (size_t)slot * t->h_block_bytes);
     const int rc = run_frame(t, img, pitch, istride);
+    if (direct_results(t)) point_results(t, t->d_rblock);      // stage entry points and fetches use the device block
     if (rc != VS_OK) return rc;
     VS_CUDA_TRY(cudaEventRecord(t->ev1, t->stream));
     prof_end(t);
@@ -733,6 +744,10 @@ static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride,
 }
 
 static int enqueue_fetch(vs_tracker* t, int slot = 0) {
+    if (direct_results(t)) {            // the frame's kernels already wrote the slot
+        VS_CUDA_TRY(cudaEventRecord(t->ev_fetch[slot], t->stream));
+        return VS_OK;
+    }
     VS_CUDA_TRY(cudaMemcpyAsync(t->h_block + (size_t)slot * t->h_block_bytes, t->d_rblock, t->h_block_bytes,
                                 cudaMemcpyDeviceToHost, t->stream));
     VS_CUDA_TRY(cudaEventRecord(t->ev_fetch[slot], t->stream));

@@ -424,11 +424,7 @@ template <int NT, bool FULLW>
 static void launch_lut_nt2(const uint8_t* src, int src_pitch, int64_t src_stride, const ClaheGeom& g, int n_streams,
                            uint8_t* luts, cudaStream_t st) {
     const int smem = 64 * NT * 4;
-    static bool configured = false;
-    if (!configured && smem > 48 * 1024) {
-        cudaFuncSetAttribute(clahe_lut_kernel<NT, FULLW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = true;
-    }
+    ensure_dyn_smem(reinterpret_cast<const void*>(clahe_lut_kernel<NT, FULLW>), smem);
     launch_pdl(clahe_lut_kernel<NT, FULLW>, dim3(kClaheTiles * kClaheTiles, n_streams), dim3(NT), smem, st,
         src, src_pitch, src_stride, g.tw, g.th, g.clip, g.lut_scale, luts);
 }

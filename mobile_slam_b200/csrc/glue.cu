@@ -751,13 +751,10 @@ void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bo
                      unsigned int seed) {
     int smem = set_mask_smem_bytes(g.cap);
     if (with_ransac && smem < g.cap * 16) smem = g.cap * 16;
-    static int configured = 0;
-    if (smem > 48 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        cudaFuncSetAttribute(post_lk_set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        cudaFuncSetAttribute(post_lk_ransac_set_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = smem;
-    }
+    const void* k = with_post_lk ? (with_ransac ? reinterpret_cast<const void*>(post_lk_ransac_set_mask_kernel)
+                                                : reinterpret_cast<const void*>(post_lk_set_mask_kernel))
+                                 : reinterpret_cast<const void*>(set_mask_kernel);
+    ensure_dyn_smem(k, smem);
     if (with_post_lk && with_ransac) launch_pdl(post_lk_ransac_set_mask_kernel, dim3(g.n_streams), dim3(256), smem, st, g, seed);
     else if (with_post_lk) launch_pdl(post_lk_set_mask_kernel, dim3(g.n_streams), dim3(256), smem, st, g);
     else launch_pdl(set_mask_kernel, dim3(g.n_streams), dim3(256), smem, st, g);
@@ -766,11 +763,7 @@ void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bo
 
 void launch_select_finish(const GlueParams& g, cudaStream_t st, int64_t* launches) {
     const int smem = kSortSmemKeys * 8 + kSelBins * 4 + g.cap * 4;
-    static int configured = 0;
-    if (configured < smem) {
-        cudaFuncSetAttribute(select_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = smem;
-    }
+    ensure_dyn_smem(reinterpret_cast<const void*>(select_finish_kernel), smem);
     launch_pdl(select_finish_kernel, dim3(g.n_streams), dim3(kFinishThreads), smem, st, g);
     if (launches) *launches += 1;
 }

@@ -545,12 +545,7 @@ int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t s
                                                                                           p.work_counters, p.work_seq & 1);
     } else {
         const int smem = kLkWarpsPerCta * lk_warp_smem(p.win);
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaFuncSetAttribute(lk_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 kLkWarpsPerCta * lk_warp_smem(kMaxWin));
-            attr_set = true;
-        }
+        ensure_dyn_smem(reinterpret_cast<const void*>(lk_kernel<0>), kLkWarpsPerCta * lk_warp_smem(kMaxWin));
         launch_pdl(lk_kernel<0>, grid, dim3(32 * kLkWarpsPerCta), smem, st, p);
     }
     if (launches) *launches += 1;

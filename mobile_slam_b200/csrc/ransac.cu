@@ -13,12 +13,8 @@ __global__ void __launch_bounds__(kRansacThreads) ransac_kernel(GlueParams g, un
 static int ransac_smem(int cap) { return cap * 16; }
 
 int launch_ransac(vs_tracker* t) {
-    static int configured = 0;
     const int smem = ransac_smem(t->cap);
-    if (smem > 48 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = smem;
-    }
+    ensure_dyn_smem(reinterpret_cast<const void*>(ransac_kernel), smem);
     launch_pdl(ransac_kernel, dim3(t->B), dim3(kRansacThreads), smem, t->stream, t->g, 12345u /* = ransac_seed() in tracker.cu */);
     t->launches += 1;
     return VS_OK;
@@ -43,12 +39,8 @@ extern "C" int vs_stage_ransac(vs_tracker* t, const float* a_xy, const float* b_
     VS_CUDA_TRY(cudaMemsetAsync(g.w_rstatus, 1, (size_t)n, t->stream));
     GlueParams g1 = g;
     g1.n_streams = 1;
-    static int configured = 0;
     const int smem = ransac_smem(t->cap);
-    if (smem > 48 * 1024 && configured < smem) {
-        cudaFuncSetAttribute(ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = smem;
-    }
+    ensure_dyn_smem(reinterpret_cast<const void*>(ransac_kernel), smem);
     ransac_kernel<<<1, kRansacThreads, smem, t->stream>>>(g1, 12345u);
     t->launches += 1;
     VS_CUDA_TRY(cudaMemcpyAsync(status, g.w_rstatus, (size_t)n, cudaMemcpyDeviceToHost, t->stream));

@@ -2,6 +2,9 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <map>
+#include <mutex>
+#include <utility>
 
 namespace vs {
 
@@ -52,6 +55,23 @@ __device__ __forceinline__ int cv_round(float v) { return __float2int_rn(v); }
 __device__ __forceinline__ void pdl_entry() {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// Opt a kernel in to more than 48 KB of dynamic shared memory.  The attribute is per device, and one process may
+// drive several GPUs (vs::ShardedTracker: one thread + handle per GPU), so what was set is remembered per
+// (kernel, device).
+inline void ensure_dyn_smem(const void* kernel, int bytes) {
+    if (bytes <= 48 * 1024) return;
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, int> done;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lock(mu);
+    int& have = done[std::make_pair(kernel, dev)];
+    if (have < bytes) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        have = bytes;
+    }
 }
 
 // Set by the frame enqueue per handle: on for few-stream (latency) handles.  For big stream batches the kernels are

@@ -124,3 +124,28 @@ def test_c4_2000_features_invariants_and_determinism(built_lib, mode):
     for a, b in zip(*runs):
         assert np.array_equal(a.ids, b.ids) and np.array_equal(a.cur_pts, b.cur_pts) and np.array_equal(a.track_cnt, b.track_cnt)
     assert len(runs[0][-1].ids) > 1500 and np.sum(runs[0][-1].track_cnt > 1) > 1200
+
+
+def test_two_gpus_in_one_process(built_lib):
+    # vs::ShardedTracker's layout: one handle per GPU inside ONE process.  Per-device kernel attributes (dynamic shared
+    # memory opt-in for the large-capacity glue kernels) must be set on every device, and a stream must give the same
+    # tracks whichever GPU it runs on.
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    cfg = dict(CONFIGS["C4"])
+    st = SynthStream(901, cfg["width"], cfg["height"], motion=2.0)
+    frames = [st.frame(k) for k in range(4)]
+    out = []
+    for dev in (0, 1):
+        tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_DEVICE, device=dev)
+        out.append((BatchTracker(tc, cam, 1), []))
+    for k, f in enumerate(frames):                      # interleaved: both devices live at the same time
+        for bt, res in out:
+            res.append(bt.track([f], [0.05 * k])[0])
+    for a, b in zip(out[0][1], out[1][1]):
+        assert np.array_equal(a.ids, b.ids) and np.array_equal(a.track_cnt, b.track_cnt)
+        assert np.array_equal(a.cur_pts, b.cur_pts) and np.array_equal(a.pts_velocity, b.pts_velocity)
+    assert len(out[0][1][-1].ids) > 1500
+    for bt, _ in out:
+        bt.close()

@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict
                 // FULLW: every tile starts on a word boundary and is a whole number of words wide, so only the
                 // past-the-end slots of the last trip (lo = 4) are invalid: one test per word instead of two per pixel
                 const uint32_t inc = (FULLW ? lo[u] == 0 : (k >= lo[u] && k < hi[u])) ? (1u << ((b >> 3) & 0x18u)) : 0u;
-                mine[(b & 63u) * NT] += inc;
+                atomicAdd(&mine[(b & 63u) * NT], inc);      // ATOMS without a result: one instruction, no load-add-store chain
             }
         }
     }

@@ -120,7 +120,9 @@ class Camera:
             if xi == 1.0:
                 return mx_u, my_u, (1.0 - mx_u * mx_u - my_u * my_u) / 2.0
             rho2 = mx_u * mx_u + my_u * my_u
-            return mx_u, my_u, 1.0 - xi * (rho2 + 1.0) / (xi + math.sqrt(1.0 + (1.0 - xi * xi) * rho2))
+            disc = 1.0 + (1.0 - xi * xi) * rho2       # negative outside the mirror's field of view: std::sqrt gives NaN
+            root = math.sqrt(disc) if disc >= 0.0 else float("nan")
+            return mx_u, my_u, 1.0 - xi * (rho2 + 1.0) / (xi + root)
         # KANNALA_BRANDT
         r = math.sqrt(mx * mx + my * my)
         phi = 0.0 if r < 1e-10 else math.atan2(my, mx)

@@ -36,3 +36,12 @@ def test_long_free_running_sequences(built_lib, name, motion, frames):
     assert r["first_divergence"] is None or r["first_divergence"] >= 60, r
     assert r["max_dpos_before_divergence"] <= 0.011, r
     assert r["pos_match_frac"] >= 0.97, r
+
+
+def test_camera_calibration_sweep(built_lib):
+    # 42 calibrations over the four camera models (pinhole incl. zero / one-sided distortion, Kannala-Brandt with every
+    # trailing-zero pattern, Mei below / at / above xi = 1, Scaramuzza), pixels inside and 40 px outside the image:
+    # float32-identical to the fp64 restatement (<= 1 ulp for Kannala-Brandt), NaN where the reference gives NaN
+    from camera_sweep import camera_sweep
+    bad = camera_sweep(verbose=False)
+    assert not bad, bad

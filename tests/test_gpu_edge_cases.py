@@ -288,3 +288,31 @@ def test_device_ransac_edge_recovery(built_lib):
     assert restored >= 1, "edge recovery never restored a point on this sequence"
     a.close()
     b.close()
+
+
+def test_ragged_batch_blank_and_busy_streams_together(built_lib):
+    # one launch covers streams in very different states: one that is featureless for 5 frames and then gets texture,
+    # one with a scene cut, a normal one, one that never has a feature.  Each must equal the same stream tracked alone.
+    cfg = dict(CONFIGS["C2"])
+    W, H = cfg["width"], cfg["height"]
+    a, b, c, d = (SynthStream(s, W, H, motion=2.0) for s in (810, 811, 812, 813))
+    flat = np.full((H, W), 90, np.uint8)
+
+    def frames(k):
+        return [flat if k < 5 else a.frame(k), (b.frame(k) if k < 4 else c.frame(k)), d.frame(k), flat]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    batch = BatchTracker(tc, cam, 4)
+    singles = [BatchTracker(tc, cam, 1) for _ in range(4)]
+    for k in range(8):
+        fr = frames(k)
+        rb = batch.track(fr, [0.05 * k] * 4)
+        for s in range(4):
+            r1 = singles[s].track([fr[s]], [0.05 * k])[0]
+            assert rb[s].ids.tolist() == r1.ids.tolist() and rb[s].track_cnt.tolist() == r1.track_cnt.tolist(), (k, s)
+            assert np.array_equal(rb[s].cur_pts, r1.cur_pts) and np.array_equal(rb[s].pts_velocity, r1.pts_velocity)
+        assert len(rb[3].ids) == 0
+        assert (len(rb[0].ids) == 0) == (k < 5)
+    assert len(rb[1].ids) > 100 and len(rb[2].ids) > 100
+    batch.close()
+    for t in singles:
+        t.close()

@@ -190,6 +190,14 @@ VS_API void* vs_tracker_cuda_stream(const struct vs_tracker* t);
  * stream synchronise per call, so it is for profiling passes, not the timed throughput region);
  * switching it on also clears the accumulators. */
 VS_API int vs_tracker_set_profiling(struct vs_tracker* t, int32_t on);
+/* The records the tracker's two callers build from its public vectors, for one stream's result:
+ *   MeasurementProcessor::extractImageFeatures (src/utility/measurement_processor.cpp:210-231): ray (x, y, 1) + channels
+ *   id, u, v, vx, vy;  VIOEngine::processFrame (src/vio_engine.cpp:219-239): common::ImageData id -> [x, y, 1, u, v, vx, vy].
+ * Only features with track_cnt > 1 are published, in array order.  ids_out[max_n], rec_out[max_n][7] doubles
+ * (x = undist.x, y = undist.y, 1, u = cur_pts.x, v = cur_pts.y, vx, vy).  Host-side, needs no GPU.  *n_out = records
+ * written; VS_ERR_CAPACITY if max_n is too small (nothing beyond max_n is written). */
+VS_API int vs_pack_image_features(const vs_track_result* r, int32_t max_n, int32_t* ids_out, double* rec_out, int32_t* n_out);
+
 /* total_ms[i] / launches[i] for kernel slot i < *n_out <= max_n; names from vs_profile_kernel_name */
 VS_API int vs_tracker_get_profile(const struct vs_tracker* t, int32_t max_n, float* total_ms, int32_t* launches,
                                   int32_t* n_out);

@@ -58,7 +58,7 @@ EXPORTS = [
     "vs_tracker_last_device_ms", "vs_stage_clahe", "vs_stage_pyramid", "vs_stage_lk",
     "vs_stage_min_eig", "vs_stage_good_features", "vs_stage_undistort", "vs_stage_set_mask",
     "vs_stage_ransac", "vs_tracker_cuda_stream", "vs_tracker_set_profiling", "vs_tracker_get_profile",
-    "vs_profile_kernel_name",
+    "vs_profile_kernel_name", "vs_pack_image_features",
 ]
 
 _lib = None
@@ -110,6 +110,9 @@ def load():
     lib.vs_tracker_cuda_stream.restype = vp
     lib.vs_tracker_set_profiling.argtypes = [vp, i32]
     lib.vs_tracker_get_profile.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(i32), C.POINTER(i32)]
+    lib.vs_pack_image_features.argtypes = [C.POINTER(VsTrackResult), i32, C.POINTER(C.c_int32), C.POINTER(C.c_double),
+                                           C.POINTER(C.c_int32)]
+    lib.vs_pack_image_features.restype = C.c_int
     lib.vs_profile_kernel_name.argtypes = [i32]
     lib.vs_profile_kernel_name.restype = C.c_char_p
     _lib = lib

@@ -999,6 +999,23 @@ int vs_tracker_get_profile(const vs_tracker* t, int32_t max_n, float* total_ms, 
     return VS_OK;
 }
 
+int vs_pack_image_features(const vs_track_result* r, int32_t max_n, int32_t* ids_out, double* rec_out, int32_t* n_out) {
+    if (!r || !ids_out || !rec_out || !n_out || max_n < 0) { set_error("vs_pack_image_features: bad argument"); return VS_ERR_INVALID; }
+    int n = 0, rc = VS_OK;
+    for (int j = 0; j < r->n; ++j) {
+        if (r->track_cnt[j] <= 1) continue;                     // measurement_processor.cpp:211
+        if (n >= max_n) { set_error("vs_pack_image_features: more than %d published features", max_n); rc = VS_ERR_CAPACITY; break; }
+        ids_out[n] = r->ids[j];
+        double* o = rec_out + 7 * (size_t)n;
+        o[0] = r->undist[2 * j];   o[1] = r->undist[2 * j + 1];   o[2] = 1.0;
+        o[3] = r->cur_pts[2 * j];  o[4] = r->cur_pts[2 * j + 1];
+        o[5] = r->velocity[2 * j]; o[6] = r->velocity[2 * j + 1];
+        ++n;
+    }
+    *n_out = n;
+    return rc;
+}
+
 const char* vs_profile_kernel_name(int32_t slot) { return (slot >= 0 && slot < PK_COUNT) ? kProfNames[slot] : ""; }
 float vs_tracker_last_device_ms(const vs_tracker* t) { return t ? t->last_ms : 0.f; }
 

@@ -62,3 +62,44 @@ def test_oracle_stdsort_is_the_real_std_sort():
     big = np.random.default_rng(0).integers(1, 4, 300).astype(np.int32)
     p = R.setmask_order(big)
     assert not np.array_equal(p, np.argsort(-big, kind="stable")), "std::sort is not stable on tie-heavy input"
+
+
+def test_pack_image_features_matches_the_callers_loop(built_lib):
+    # vs_pack_image_features = the loop of MeasurementProcessor::extractImageFeatures (measurement_processor.cpp:210-231)
+    # and VIOEngine::processFrame (vio_engine.cpp:219-239): only track_cnt > 1, array order, [x, y, 1, u, v, vx, vy]
+    import ctypes as C
+    import numpy as np
+    from mobile_slam_b200 import _abi
+    lib = _abi.load()
+    rng = np.random.default_rng(3)
+    n = 37
+    ids = np.arange(100, 100 + n, dtype=np.int32)
+    cnt = rng.integers(1, 5, n).astype(np.int32)
+    pts = rng.uniform(0, 700, (n, 2)).astype(np.float32)
+    un = rng.uniform(-1, 1, (n, 2)).astype(np.float32)
+    vel = rng.uniform(-3, 3, (n, 2)).astype(np.float32)
+    r = _abi.VsTrackResult()
+    r.n, r.n_new = n, 0
+    r.ids = ids.ctypes.data_as(C.POINTER(C.c_int32))
+    r.track_cnt = cnt.ctypes.data_as(C.POINTER(C.c_int32))
+    r.cur_pts = pts.ctypes.data_as(C.POINTER(C.c_float))
+    r.undist = un.ctypes.data_as(C.POINTER(C.c_float))
+    r.velocity = vel.ctypes.data_as(C.POINTER(C.c_float))
+    out_ids = np.zeros(n, np.int32)
+    rec = np.zeros((n, 7), np.float64)
+    m = C.c_int32(0)
+    rc = lib.vs_pack_image_features(C.byref(r), n, out_ids.ctypes.data_as(C.POINTER(C.c_int32)),
+                                    rec.ctypes.data_as(C.POINTER(C.c_double)), C.byref(m))
+    assert rc == 0
+    keep = cnt > 1
+    assert m.value == int(keep.sum())
+    assert out_ids[:m.value].tolist() == ids[keep].tolist()
+    want = np.concatenate([un[keep], np.ones((m.value, 1), np.float32), pts[keep], vel[keep]], 1).astype(np.float64)
+    assert np.array_equal(rec[:m.value], want)
+    # too small a buffer: error code, nothing written past it
+    small = np.zeros((2, 7), np.float64)
+    sid = np.zeros(2, np.int32)
+    rc = lib.vs_pack_image_features(C.byref(r), 2, sid.ctypes.data_as(C.POINTER(C.c_int32)),
+                                    small.ctypes.data_as(C.POINTER(C.c_double)), C.byref(m))
+    assert rc == _abi.VS_ERR_CAPACITY if hasattr(_abi, "VS_ERR_CAPACITY") else rc == -4
+    assert m.value == 2 and np.array_equal(small, want[:2])

@@ -45,3 +45,13 @@ def test_camera_calibration_sweep(built_lib):
     from camera_sweep import camera_sweep
     bad = camera_sweep(verbose=False)
     assert not bad, bad
+
+
+def test_soak_submit_wait_and_handle_lifecycle(built_lib):
+    # 600 batches through submit/wait on a 2-lane handle with the device RANSAC, then 60 create/track/destroy cycles:
+    # no error, no collapse of the published feature count, no device-memory growth (scripts/soak.py asserts them)
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "soak.py"), "600", "8"], capture_output=True, text=True,
+                       timeout=600, cwd=root)
+    assert r.returncode == 0 and "soak ok" in r.stdout, r.stdout[-800:] + r.stderr[-800:]

@@ -624,7 +624,7 @@ def main():
     ap.add_argument("--dev-lanes", type=int, default=1, help="pipeline lanes of the device-resident handle")
     ap.add_argument("--max-frames", type=int, default=32, help="distinct frames buffered per stream")
     ap.add_argument("--latency-frames", type=int, default=200)
-    ap.add_argument("--cpu-frames", type=int, default=60, help="cpu_baseline sample: frames per process")
+    ap.add_argument("--cpu-frames", type=int, default=150, help="cpu_baseline sample: frames per process (about 25 s of CPU work on 16 cores)")
     ap.add_argument("--cpu-frames-per-step", type=int, default=4)
     ap.add_argument("--cpu-procs", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")

@@ -28,7 +28,7 @@ if os.path.exists(lat):
 src = os.path.join(go, f"{tag}_launches.csv")
 if os.path.exists(src):
     open(os.path.join(pr, f"{tag}_launches.csv"), "w").write(open(src).read())
-for f in ("c2", "c1", "ref"):
+for f in ("c2", "c1", "c3", "c4", "ref"):
     p = os.path.join(go, f"{tag}_bench_{f}.json")
     if os.path.exists(p) and os.path.getsize(p):
         d = json.loads(open(p).read().strip().splitlines()[-1])

@@ -112,3 +112,18 @@ def test_sequence_golden(built_lib, fname, key):
         dv = np.abs(np.asarray(ft.pts_velocity)[a] - q[f"vel{k}"][b]).max()
         assert dv <= 0.01 / 0.05 * 2, dv          # velocity = delta undist / dt: 0.01 px error bound scaled
     assert n_common >= 0.99 * n_ref, (n_common, n_ref)
+
+
+def test_two_pixel_lane_variant_golden(built_lib):
+    """shi_tomasi_kernel<2, .> (VS_ST_PX=2, read once per process): the same golden corner lists, eig map and
+    free-running sequences through the two-pixels-per-lane build of the strip walk."""
+    import subprocess
+    import sys
+    if os.environ.get("VS_ST_PX") == "2":
+        pytest.skip("already inside the VS_ST_PX=2 run")
+    env = dict(os.environ, VS_ST_PX="2")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-k",
+                        "good_features_golden or min_eig_golden or sequence_golden"],
+                       env=env, capture_output=True, text=True, timeout=600, cwd=os.path.dirname(GOLD))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout

@@ -68,7 +68,8 @@ __device__ __forceinline__ void post_lk_body(const GlueParams& g, const int s, c
             g.w_cnt[o + slot] = g.cnt[o + i] + 1;
             g.w_un[o + slot] = g.un[o + i];
             g.w_rstatus[o + slot] = 1;
-            const double dx = (double)nx.x - (double)cur.x, dy = (double)nx.y - (double)cur.y;
+            // float - float, then widened: `double dx = next_pts[i].x - cur_pts[i].x;` (feature_tracker.cpp:161-162)
+            const double dx = (double)__fsub_rn(nx.x, cur.x), dy = (double)__fsub_rn(nx.y, cur.y);
             acc += dx * dx + dy * dy;
         }
     }

@@ -169,7 +169,8 @@ class RefFeatureTracker:
         # ft:156-173
         should_reject = True
         if len(self.next_pts) > 0 and len(self.cur_pts) == len(self.next_pts):
-            d = self.next_pts.astype(np.float64) - self.cur_pts.astype(np.float64)
+            # ft:161-162: `double dx = next_pts[i].x - cur_pts[i].x;` — a float32 subtraction, widened afterwards
+            d = (self.next_pts.astype(np.float32) - self.cur_pts.astype(np.float32)).astype(np.float64)
             rms = np.sqrt((d * d).sum() / len(self.next_pts))
             if rms < 2.0:
                 should_reject = False

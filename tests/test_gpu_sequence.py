@@ -59,6 +59,7 @@ def test_sequence_parity_no_ransac(built_lib, name, n_frames):
     assert stats["cnt_equal"] >= 0.995 * stats["common"], stats
     assert stats["max_dpos"] <= 0.01, stats
     assert stats["max_dun"] <= 1e-4, stats
+    assert stats["max_dvel"] <= 2 * 1e-4 / 0.05, stats     # velocity = delta undist / dt (dt = 0.05 s)
     assert exact_frames >= int(0.9 * n_frames), f"{exact_frames}/{n_frames} frames identical (ids+track_cnt); {stats}"
     assert len(ft.image_data()) > 0.5 * cfg["max_cnt"]
 
@@ -92,6 +93,7 @@ def test_sequence_parity_with_cv_ransac_callback(built_lib):
     frac = stats["common"] / max(stats["ref"], 1)
     assert frac >= 0.97, stats          # RANSAC flips on 1e-3 px input noise (SURVEY.md §7 hard part 4)
     assert stats["max_dpos"] <= 0.01, stats
+    assert stats["max_dvel"] <= 2 * 1e-4 / 0.05, stats
     bt.close()
 
 

@@ -19,8 +19,16 @@ Printed JSON line (rank 0):
   cpu_baseline   the reference's OpenCV CPU tracker (oracle/cv_reference.py over cv2) on a bounded sample
   clocks         nvidia-smi SM clocks / throttle reasons sampled during the timed regions
 
-`--impl reference` times only the CPU tracker (one process per host core, one stream each).
-Nothing here reads /root/reference.
+  c1             compact sub-record (value / e2e / dominant-kernel roofline) of the other shape the 70 % target names
+                 (C1, 512x512 TUM-VI) — only in the default C2 line
+
+`--config C5` = BASELINE.json configs[4] as written: 64 independent C1 streams IN TOTAL, sharded s mod N over the N
+ranks (64 / 32 / 16 / 8 streams per GPU): "scaling": "strong".  Every other config is weak scaling (S streams per GPU).
+
+`--impl reference` times only the CPU tracker (one process per host core, one stream each): the reference's own
+feature_tracker.cpp compiled into oracle/_ref/libvsref.so (OpenCV calls served by the cv2 wheel) when that library
+was shipped, else the Python port of it.  Both arms track the SAME frames (the GPU arm's synthetic streams 0..P-1,
+dumped to host).  Nothing here reads /root/reference.
 """
 from __future__ import annotations
 
@@ -244,17 +252,33 @@ def bounce(i: int, n: int) -> int:
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the reference's OpenCV tracker, one process per core, one stream per process
 # --------------------------------------------------------------------------------------------------
-def _cpu_worker(args):
-    cfg_name, sid, n_frames, n_warm, threads, use_ransac = args
-    import cv2
-    cv2.setNumThreads(threads)
-    from mobile_slam_b200.synth import SynthStream
+def _make_cpu_tracker(cfg, use_ransac):
+    """(tracker, kind): the compiled reference tracker (oracle/_ref) when shipped, else the Python port."""
     from oracle import camera as ocam
     from oracle import cv_reference as R
+    try:
+        from oracle import ref_binding as RB
+        if RB.available():
+            return RB.CompiledRefTracker(R.config_from_synth(cfg, use_ransac=use_ransac), ocam.from_config(cfg)), "reference"
+    except Exception:  # noqa: BLE001 - fall back to the port
+        pass
+    return R.RefFeatureTracker(R.config_from_synth(cfg, use_ransac=use_ransac), ocam.from_config(cfg)), "port"
+
+
+def _cpu_worker(args):
+    cfg_name, sid, n_frames, n_warm, threads, use_ransac, frames_path = args
+    import cv2
+    cv2.setNumThreads(threads)
     cfg = CONFIGS[cfg_name]
-    st = SynthStream(1000 + sid, cfg["width"], cfg["height"])
-    frames = [st.frame(k) for k in range(n_warm + n_frames)]
-    ref = R.RefFeatureTracker(R.config_from_synth(cfg, use_ransac=use_ransac), ocam.from_config(cfg))
+    if frames_path:
+        # the GPU arm's own frames of stream `sid` (n_buf, H, W), walked in the GPU arm's order
+        buf = np.load(frames_path, mmap_mode="r")[:, sid]
+        frames = [np.ascontiguousarray(buf[bounce(k, buf.shape[0])]) for k in range(n_warm + n_frames)]
+    else:
+        from mobile_slam_b200.synth import SynthStream
+        st = SynthStream(1000 + sid, cfg["width"], cfg["height"])
+        frames = [st.frame(k) for k in range(n_warm + n_frames)]
+    ref, kind = _make_cpu_tracker(cfg, use_ransac)
     feats = 0
     for k in range(n_warm):
         ref.detect_and_track(frames[k], 0.05 * k)
@@ -265,14 +289,14 @@ def _cpu_worker(args):
         ref.update_all_ids()
         feats += sum(1 for c in ref.track_cnt if c > 1)
     dt = time.perf_counter() - t0
-    return dt, n_frames, feats
+    return dt, n_frames, feats, kind
 
 
-def cpu_tracker_throughput(cfg_name, frames_per_proc, procs, warm=3, threads=1, use_ransac=False):
+def cpu_tracker_throughput(cfg_name, frames_per_proc, procs, warm=3, threads=1, use_ransac=False, frames_path=None):
     """frames/s of `procs` independent CPU trackers running concurrently (one stream each)."""
     import multiprocessing as mp
     ctx = mp.get_context("spawn")
-    jobs = [(cfg_name, s, frames_per_proc, warm, threads, use_ransac) for s in range(procs)]
+    jobs = [(cfg_name, s, frames_per_proc, warm, threads, use_ransac, frames_path) for s in range(procs)]
     if procs == 1:
         res = [_cpu_worker(jobs[0])]
     else:
@@ -281,7 +305,20 @@ def cpu_tracker_throughput(cfg_name, frames_per_proc, procs, warm=3, threads=1, 
     tmax = max(r[0] for r in res)
     frames = sum(r[1] for r in res)
     feats = sum(r[2] for r in res)
-    return frames / tmax, feats / tmax, tmax
+    return frames / tmax, feats / tmax, tmax, res[0][3]
+
+
+def cpu_kind_text(kind):
+    return ("oracle/_ref/libvsref.so = the reference's feature_tracker.cpp compiled, OpenCV calls served by cv2 " + cv2_version()
+            if kind == "reference" else "oracle/cv_reference.py (Python port of feature_tracker.cpp) over cv2 " + cv2_version())
+
+
+def dump_frames_for_cpu(h_frames_np, n_streams_wanted):
+    """streams 0..P-1 of the GPU arm's host frame buffer -> a .npy the CPU workers map (identical frames, both arms)."""
+    import tempfile
+    path = os.path.join(tempfile.gettempdir(), f"vs_bench_frames_{os.getpid()}.npy")
+    np.save(path, np.ascontiguousarray(h_frames_np[:, :n_streams_wanted]))
+    return path
 
 
 def run_reference(args, rank, world):
@@ -290,22 +327,42 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     procs = max(1, min(cores, args.cpu_procs or cores))
     per_step = args.cpu_frames_per_step
+    cfg_name = "C1" if args.config == "C5" else args.config
+    cfg = CONFIGS[cfg_name]
     # every process tracks (warmup + steps) * per_step frames of its own stream; the first warmup*per_step untimed
     n_warm = args.warmup * per_step
     n_timed = args.steps * per_step
-    fps, feats, tmax = cpu_tracker_throughput(args.config, n_timed, procs, warm=n_warm, threads=1,
-                                              use_ransac=bool(args.ransac))
-    cfg = CONFIGS[args.config]
+    # the same frames as the GPU arm: its synthetic streams are generated with torch on the device (data generation, not
+    # the path under test), so regenerate them the same way when a GPU is visible and hand streams 0..procs-1 to the workers
+    frames_path, frames_src = None, "mobile_slam_b200.synth.SynthStream (no CUDA device visible: NOT the GPU arm's frames)"
+    try:
+        import torch
+        if torch.cuda.is_available():
+            S = 64 if args.config == "C5" else args.streams
+            dev = torch.device("cuda", 0)
+            n_buf = min(args.steps + max(args.warmup, 3) + 1, args.max_frames)
+            st = DeviceStreams(S, cfg["width"], cfg["height"], dev, seed=1234)
+            host = np.stack([st.frame(k)[:procs].cpu().numpy() for k in range(n_buf)])
+            del st
+            torch.cuda.empty_cache()
+            frames_path = dump_frames_for_cpu(host, procs)
+            frames_src = f"the GPU arm's DeviceStreams(seed 1234) streams 0..{procs - 1}, {n_buf} frames walked back and forth"
+    except Exception as e:  # noqa: BLE001
+        frames_src += f" ({type(e).__name__})"
+    fps, feats, tmax, kind = cpu_tracker_throughput(cfg_name, n_timed, procs, warm=n_warm, threads=1,
+                                                    use_ransac=bool(args.ransac), frames_path=frames_path)
+    if frames_path:
+        os.unlink(frames_path)
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tmax / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32/f32",
-        "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong" if args.config == "C5" else "weak", "vs_baseline": None,
+        "dtype": "u8/int32/f32", "data": "synthetic",
         "config": workload_config(args, cfg, None),
         "features_per_s": feats,
-        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": procs, "kind": "port",
-                         "sample": f"{procs} processes x {n_timed} frames, one synthetic {args.config} stream each, "
-                                   f"cv2 {cv2_version()} single-threaded per process; a step = {per_step} frames per process"},
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": procs, "kind": kind,
+                         "sample": f"{procs} processes x {n_timed} frames, one stream each, {cpu_kind_text(kind)}, single-threaded "
+                                   f"per process; a step = {per_step} frames per process; frames: {frames_src}"},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -319,93 +376,118 @@ def cv2_version():
         return "missing"
 
 
-def workload_config(args, cfg, streams):
+C5_TOTAL_STREAMS = 64      # BASELINE.json configs[4]: 64 independent synthetic 512x512 streams in total
+
+
+def workload_config(args, cfg, streams, name=None):
+    name = name or args.config
     lv = level_sizes(cfg["width"], cfg["height"], cfg["max_level"])
+    shape = (f"{cfg['width']}x{cfg['height']} mono, max_cnt {cfg['max_cnt']}, min_dist {cfg['min_dist']}, "
+             f"LK win {LK_WIN} maxLevel {cfg['max_level']} ({len(lv)} levels), camera {cfg['model']}")
+    if name == "C5":
+        wl = f"C5: {C5_TOTAL_STREAMS} independent C1 streams in total, stream s on GPU s mod N; C1 = {shape}"
+        par = f"{C5_TOTAL_STREAMS} streams sharded over {args.gpus} GPU(s) (strong scaling), no collective"
+    else:
+        wl = f"{name}: {shape}"
+        par = f"stream-sharded x{args.gpus}, no collective"
     return {
-        "workload": f"{args.config}: {cfg['width']}x{cfg['height']} mono, max_cnt {cfg['max_cnt']}, min_dist {cfg['min_dist']}, "
-                    f"LK win {LK_WIN} maxLevel {cfg['max_level']} ({len(lv)} levels), camera {cfg['model']}",
+        "workload": wl,
         "streams_per_gpu": streams, "ransac": ("on: device 7-point RANSAC in this arm, cv2.findFundamentalMat in the CPU arms" if args.ransac
                                               else "off (both arms)"),
         "e2e_pipeline_lanes": args.lanes,
-        "parallelism": f"stream-sharded x{args.gpus}, no collective",
+        "parallelism": par,
     }
+
+
+def merged_traffic():
+    """kernel -> (dram bytes per stream, file): newest committed ncu capture per kernel over profiles/*_traffic.json."""
+    import glob
+    out = {}
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json"))):
+        try:
+            tj = json.load(open(f))
+        except Exception:  # noqa: BLE001
+            continue
+        if not str(tj.get("workload", "")).startswith("C2"):
+            continue
+        for k, v in tj.get("kernels", {}).items():
+            out[k] = (v["dram_bytes_per_stream"], os.path.basename(f))     # later files (sorted by round tag) win
+    return out
 
 
 # --------------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------------
-def run_ours(args, rank, world, local_rank):
-    import torch
-    import torch.distributed as dist
-    from mobile_slam_b200 import BatchTracker, VS_RANSAC_DEVICE, VS_RANSAC_OFF, config_from_synth
+class Dist:
+    """barrier / reductions over the ranks (NCCL is used for nothing else: the path has no data collective)."""
 
-    # NUMA: run this rank (and first-touch its pinned frame buffers) on the cores next to its GPU, otherwise every rank's
-    # host->device traffic crosses the socket interconnect from node 0
-    numa_cpus = None
-    orig_affinity = os.sched_getaffinity(0)
-    try:
-        import pynvml
-        pynvml.nvmlInit()
-        hnd = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
-        words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (os.cpu_count() + 63) // 64)
-        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
-        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
-        if cpus:
-            os.sched_setaffinity(0, cpus)
-            numa_cpus = len(cpus)
-    except Exception:  # noqa: BLE001 - affinity is an optimisation only
-        pass
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    def __init__(self, world, dev):
+        self.world, self.dev = world, dev
 
-    def barrier():
-        if world > 1:
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(v: float) -> float:
-        if world == 1:
-            return v
-        t = torch.tensor([v], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    def _red(self, v, op):
+        import torch
+        import torch.distributed as dist
+        if self.world == 1:
+            return float(v)
+        t = torch.tensor([float(v)], device=self.dev, dtype=torch.float64)
+        dist.all_reduce(t, op=op)
         return float(t.item())
 
-    def sum_over_ranks(v: float) -> float:
-        if world == 1:
-            return v
-        t = torch.tensor([v], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    def max(self, v):
+        import torch.distributed as dist
+        return self._red(v, dist.ReduceOp.MAX)
 
-    cfg = CONFIGS[args.config]
-    S, W, H = args.streams, cfg["width"], cfg["height"]
+    def sum(self, v):
+        import torch.distributed as dist
+        return self._red(v, dist.ReduceOp.SUM)
+
+
+def measure(args, name, rank, world, local_rank, D, clocks, compact=False):
+    """One workload on this rank's GPU: device-resident throughput, per-kernel profile, e2e (host frames), latency.
+    Returns the aggregated numbers (identical on every rank) plus this rank's host frame buffer."""
+    import ctypes as C
+    import torch
+    from mobile_slam_b200 import BatchTracker, VS_RANSAC_DEVICE, VS_RANSAC_OFF, config_from_synth, sharding
+    dev = D.dev
+    cfg = CONFIGS["C1" if name == "C5" else name]
+    W, H = cfg["width"], cfg["height"]
     K, Wm = args.steps, args.warmup
     n_buf = min(K + Wm + 1, args.max_frames)
-    streams = DeviceStreams(S, W, H, dev, seed=1234 + 7919 * rank)
+    if name == "C5":
+        mine = sharding.streams_of_rank(C5_TOTAL_STREAMS, rank, world)           # global ids s with s mod N == rank
+        streams = DeviceStreams(C5_TOTAL_STREAMS, W, H, dev, seed=1234)           # the same 64 streams whatever N is
+        S = len(mine)
+        sel = torch.tensor(mine, device=dev)
+    else:
+        S = args.streams
+        mine = [rank + world * i for i in range(S)]
+        streams = DeviceStreams(S, W, H, dev, seed=1234 + 7919 * rank)
+        sel = None
     d_frames = torch.empty((n_buf, S, H, W), device=dev, dtype=torch.uint8)
     for k in range(n_buf):
-        d_frames[k] = streams.frame(k)
+        f = streams.frame(k)
+        d_frames[k] = f if sel is None else f[sel]
     del streams
     torch.cuda.empty_cache()
     h_frames = torch.empty((n_buf, S, H, W), dtype=torch.uint8, pin_memory=True)
     h_frames.copy_(d_frames)
     torch.cuda.synchronize()
     step_bytes = S * H * W
-
     mode = VS_RANSAC_DEVICE if args.ransac else VS_RANSAC_OFF
     tc, cam = config_from_synth(cfg, ransac_mode=mode, device=local_rank)
-    import ctypes as C
-
-    clocks = ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
 
     def times(i):
         return (C.c_double * S)(*([0.05 * i] * S))
 
-    # ---- (1) device-resident throughput: CUDA events on the handle's own stream ----
+    # ---- (1) device-resident throughput: CUDA events on the handle's own stream; the K-step region is repeated
+    #          `--repeats` times and the MEDIAN repeat is reported (a single 20-step region is ~50 ms) ----
     tc.pipeline_lanes = args.dev_lanes
     bt = BatchTracker(tc, cam, S)
     ext = torch.cuda.ExternalStream(bt.cuda_stream, device=dev)
@@ -413,23 +495,27 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(Wm):
         bt.track_device(d_frames[bounce(step, n_buf)].data_ptr(), W, H * W, times(step), to_host=False)
         step += 1
-    barrier()
-    l0 = bt.launch_count
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    clocks.region(True)
-    e0.record(ext)
-    for _ in range(K):
-        bt.track_device(d_frames[bounce(step, n_buf)].data_ptr(), W, H * W, times(step), to_host=False)
-        step += 1
-    e1.record(ext)
-    e1.synchronize()
-    clocks.region(False)
-    barrier()
-    dev_ms = max_over_ranks(e0.elapsed_time(e1))
-    launches = bt.launch_count - l0
+    reps = 1 if compact else max(1, args.repeats)
+    rep_ms, launches = [], 0
+    for _ in range(reps):
+        D.barrier()
+        l0 = bt.launch_count
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        clocks.region(True)
+        e0.record(ext)
+        for _ in range(K):
+            bt.track_device(d_frames[bounce(step, n_buf)].data_ptr(), W, H * W, times(step), to_host=False)
+            step += 1
+        e1.record(ext)
+        e1.synchronize()
+        clocks.region(False)
+        D.barrier()
+        rep_ms.append(D.max(e0.elapsed_time(e1)))
+        launches = bt.launch_count - l0
+    dev_ms = float(np.median(rep_ms))
     res = bt.fetch()
-    n_feat_mean = float(np.mean([len(r.ids) for r in res]))
-    pub_mean = float(np.mean([int(np.sum(r.track_cnt > 1)) for r in res]))
+    n_feat_mean = D.sum(float(np.sum([len(r.ids) for r in res]))) / D.sum(float(S))
+    pub_mean = D.sum(float(np.sum([int(np.sum(r.track_cnt > 1)) for r in res]))) / D.sum(float(S))
 
     # ---- (2) per-kernel CUDA events (profiling pass, same workload) ----
     bt.set_profiling(True)
@@ -438,25 +524,27 @@ def run_ours(args, rank, world, local_rank):
         step += 1
     prof = bt.profile()
     bt.set_profiling(False)
+    bt.close()
 
     # ---- (3) end to end through the C ABI with host frames: the handle is split into pipeline lanes so the H2D copy
-    #          of one lane's frames overlaps the kernels of another (all inside the one synchronous call) ----
-    bt.close()
+    #          of one lane's frames overlaps the kernels of another ----
     tc.pipeline_lanes = args.lanes
     bt = BatchTracker(tc, cam, S)
     step = 0
     for _ in range(Wm):
         bt.track_pinned(h_frames[bounce(step, n_buf)].data_ptr(), H * W, times(step))
         step += 1
-    barrier()
-    # (3a) synchronous calls, one after the other
-    t0 = time.perf_counter()
-    for _ in range(K):
-        bt.track_pinned(h_frames[bounce(step, n_buf)].data_ptr(), H * W, times(step))
-        step += 1
-    torch.cuda.synchronize()
-    e2e_sync_s = max_over_ranks(time.perf_counter() - t0)
-    barrier()
+    D.barrier()
+    e2e_sync_s = None
+    if not compact:
+        # (3a) synchronous calls, one after the other
+        t0 = time.perf_counter()
+        for _ in range(K):
+            bt.track_pinned(h_frames[bounce(step, n_buf)].data_ptr(), H * W, times(step))
+            step += 1
+        torch.cuda.synchronize()
+        e2e_sync_s = D.max(time.perf_counter() - t0)
+        D.barrier()
     # (3b) submit / wait with two batches in flight (upload of batch k+1 overlaps the kernels of batch k): the headline
     clocks.region(True)
     t0 = time.perf_counter()
@@ -470,24 +558,49 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     clocks.region(False)
-    barrier()
-    e2e_s = max_over_ranks(e2e_s)
+    last = bt._collect()              # numpy views of the last batch's results (outside the timed region)
+    D.barrier()
+    e2e_s = D.max(e2e_s)
     d2h_bytes = S * (16 * 4 + bt.capacity * 32)
+    # (3c) the final host-side gather of the per-stream tracks north_star names (the only cross-rank exchange of the
+    #      path): once per step in a deployment that wants all tracks in one place; timed on its own, max over ranks
+    gather_ms = None
+    total_S = int(D.sum(float(S)))
+    if world > 1:
+        D.barrier()
+        t0 = time.perf_counter()
+        merged = sharding.gather_tracks(mine, last, dst=0)
+        gather_ms = D.max(1e3 * (time.perf_counter() - t0))
+        if rank == 0 and (merged is None or len(merged) != total_S):
+            raise RuntimeError(f"gather_tracks returned {0 if merged is None else len(merged)} streams, expected {total_S}")
     bt.close()
-    # what the link alone allows: one step's frames, pinned host -> device, nothing else running
-    pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    d_frames[0].copy_(h_frames[0], non_blocking=True)
-    torch.cuda.synchronize()
-    pe0.record()
-    for i in range(4):
-        d_frames[i % n_buf].copy_(h_frames[i % n_buf], non_blocking=True)
-    pe1.record()
-    pe1.synchronize()
-    h2d_gbs = 4 * step_bytes / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+    # what the link alone allows: one step's frames, pinned host -> device; solo on rank 0's GPU first, then with every
+    # rank copying at once (shared PCIe switches / host memory show up as the difference)
+    def h2d_rate(reps_=4):
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        d_frames[0].copy_(h_frames[0], non_blocking=True)
+        torch.cuda.synchronize()
+        pe0.record()
+        for i in range(reps_):
+            d_frames[i % n_buf].copy_(h_frames[i % n_buf], non_blocking=True)
+        pe1.record()
+        pe1.synchronize()
+        return reps_ * step_bytes / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+    D.barrier()
+    solo = [0.0] * world
+    for r in range(world):            # one rank at a time
+        if r == rank:
+            solo[r] = h2d_rate()
+        D.barrier()
+    h2d_solo = [D.sum(v) for v in solo] if world > 1 else solo
+    D.barrier()
+    h2d_all = h2d_rate(8)             # every rank at once
+    D.barrier()
+    h2d_all_sum, h2d_all_min = D.sum(h2d_all), -D.max(-h2d_all)
 
     # ---- (4) single-stream latency ----
     lat = None
-    if rank == 0:
+    if rank == 0 and not compact:
         def one_stream_latency(tc1):
             bt1 = BatchTracker(tc1, cam, 1)
             ts1 = []
@@ -510,36 +623,30 @@ def run_ours(args, rank, world, local_rank):
             tc_off.pipeline_lanes = tc.pipeline_lanes
             lat["ransac_off_p50"] = one_stream_latency(tc_off)["p50"]
 
-    total_frames = sum_over_ranks(float(S * K))
-    value = total_frames / (dev_ms * 1e-3)
-    e2e_value = total_frames / e2e_s
+    total_frames = D.sum(float(S * K))
+    S_max = int(D.max(float(S)))
+    out = dict(name=name, cfg=cfg, S=S, S_max=S_max, total_frames=total_frames, dev_ms=dev_ms, rep_ms=rep_ms,
+               launches=int(launches), prof=prof, e2e_s=e2e_s, e2e_sync_s=e2e_sync_s, d2h_bytes=d2h_bytes,
+               step_bytes=step_bytes, gather_ms=gather_ms, h2d_solo=h2d_solo, h2d_all_sum=h2d_all_sum,
+               h2d_all_min=h2d_all_min, lat=lat, n_feat_mean=n_feat_mean, pub_mean=pub_mean, n_buf=n_buf,
+               value=total_frames / (dev_ms * 1e-3), e2e_value=total_frames / e2e_s, h_frames=h_frames)
+    return out
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
 
-    # ---- roofline per kernel ----
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak = float(json.load(open(peaks_path))["hbm_gbs"])
-        peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)"
-    else:
-        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-    alg = algorithmic_bytes(cfg, n_feat=n_feat_mean)
-    kernels = {}
-    stage_ms = {}
-    step_prof_ms = 0.0
-    for name, (ms, cnt) in prof.items():
+def roofline_of(m, K, world, peak, peak_src):
+    """per-kernel / per-stage roofline of one measure() record: algorithmic bytes per launch (SURVEY.md §8d figure x the
+    streams one launch processes on ONE GPU) / CUDA-event duration, against the measured HBM peak of one GPU."""
+    cfg, S = m["cfg"], m["S_max"]
+    alg = algorithmic_bytes(cfg, n_feat=m["n_feat_mean"])
+    kernels, stage_ms, step_prof_ms = {}, {}, 0.0
+    for kname, (ms, cnt) in m["prof"].items():
         if cnt == 0:
             continue
-        per_launch = ms / cnt
         step_prof_ms += ms / K
-        kernels[name] = {"ms_per_step": ms / K, "launch_groups": cnt}
-        st = STAGE_OF_SLOT.get(name)
+        kernels[kname] = {"ms_per_step": ms / K, "launch_groups": cnt}
+        st = STAGE_OF_SLOT.get(kname)
         if st:
             stage_ms[st] = stage_ms.get(st, 0.0) + ms / K
-        del per_launch
     stages = {}
     for st, ms in stage_ms.items():
         b = alg[st] * S
@@ -547,65 +654,137 @@ def run_ours(args, rank, world, local_rank):
         stages[st] = {"alg_bytes_per_step": b, "ms_per_step": ms, "achieved_gbs": ach, "frac": ach / peak}
     dom = max(kernels.items(), key=lambda kv: kv[1]["ms_per_step"])[0]
     dom_stage = STAGE_OF_SLOT.get(dom, dom)
+    roofline = {"kernel": dom, "bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
+                "traffic": None, "peak_source": peak_src}
     if dom_stage in stages:
         d = stages[dom_stage]
-        roofline = {"kernel": dom, "bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                    "frac": d["frac"], "traffic": None, "peak_source": peak_src,
-                    "alg_bytes_per_launch": d["alg_bytes_per_step"], "ms_per_launch": d["ms_per_step"]}
-    else:
-        roofline = {"kernel": dom, "bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
-                    "traffic": None, "peak_source": peak_src}
-    frame_frac = alg["frame"] * value / 1e9 / peak
-    # measured DRAM traffic of the dominant kernel (one `ncu --set full` capture, committed under profiles/): per-stream
-    # bytes of that capture x the streams of this launch.  Only valid for the workload the capture was taken on.
-    try:
-        import glob
-        tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))
-        if tfiles and args.config == "C2":
-            tj = json.load(open(tfiles[-1]))
-            tk = tj["kernels"].get(dom_stage)
-            if tk:
-                roofline["traffic"] = tk["dram_bytes_per_stream"] * S
-                roofline["traffic_source"] = os.path.basename(tfiles[-1])
-    except Exception:  # noqa: BLE001 - the roofline stands without it
-        pass
+        roofline.update(achieved=d["achieved_gbs"], frac=d["frac"], alg_bytes_per_launch=d["alg_bytes_per_step"],
+                        ms_per_launch=d["ms_per_step"])
+    # measured DRAM traffic (one `ncu --set full` capture per kernel, committed under profiles/): per-stream bytes of that
+    # capture x the streams of this launch.  Captures are of the C2 workload only.
+    if m["name"] == "C2":
+        tr = merged_traffic()
+        for st, d in stages.items():
+            if st in tr:
+                d["traffic"] = tr[st][0] * S
+                d["traffic_over_alg"] = d["traffic"] / d["alg_bytes_per_step"]
+                d["traffic_source"] = tr[st][1]
+        if dom_stage in stages and "traffic" in stages[dom_stage]:
+            roofline.update(traffic=stages[dom_stage]["traffic"], traffic_over_alg=stages[dom_stage]["traffic_over_alg"],
+                            traffic_source=stages[dom_stage]["traffic_source"])
+    # whole frame: bytes of all frames of the job per second, against the HBM peak of ALL the GPUs that moved them
+    frame_frac = alg["frame"] * m["value"] / 1e9 / (peak * world)
+    return dict(roofline=roofline, stages=stages, kernels=kernels, profiled_ms_per_step=step_prof_ms,
+                frame_hbm_frac=frame_frac, alg_bytes_per_frame=alg["frame"])
 
-    # ---- CPU baseline on this box's host cores (bounded sample) ----
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    # NUMA: run this rank (and first-touch its pinned frame buffers) on the cores next to its GPU, otherwise every rank's
+    # host->device traffic crosses the socket interconnect from node 0
+    numa_cpus = None
+    orig_affinity = os.sched_getaffinity(0)
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        hnd = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            numa_cpus = len(cpus)
+    except Exception:  # noqa: BLE001 - affinity is an optimisation only
+        pass
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    D = Dist(world, dev)
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    K, Wm = args.steps, args.warmup
+
+    m = measure(args, args.config, rank, world, local_rank, D, clocks)
+    m1 = None
+    if args.config == "C2" and not args.no_c1:
+        # the other shape the 70 % target names, so that the driver-run line covers both (compact: no latency probe, no
+        # synchronous-call e2e, one timed repeat)
+        m1 = measure(args, "C1", rank, world, local_rank, D, clocks, compact=True)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak = float(json.load(open(peaks_path))["hbm_gbs"])
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    R = roofline_of(m, K, world, peak, peak_src)
+    cfg, S, H, W = m["cfg"], m["S"], m["cfg"]["height"], m["cfg"]["width"]
+
+    # ---- CPU baseline on this box's host cores (bounded sample), on the GPU arm's own frames ----
     cpu = None
     if not args.no_cpu:
         os.sched_setaffinity(0, orig_affinity)          # the CPU arm gets every host core back
         cores = os.cpu_count() or 1
-        fps1, feats1, t1 = cpu_tracker_throughput(args.config, args.cpu_frames, 1, threads=1, use_ransac=bool(args.ransac))
-        fpsN, featsN, tN = cpu_tracker_throughput(args.config, args.cpu_frames, cores, threads=1,
-                                                  use_ransac=bool(args.ransac))
-        cpu = {"value": fpsN, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{cores} processes x {args.cpu_frames} frames of one synthetic {args.config} stream each "
-                         f"(cv2 {cv2_version()}, 1 thread per process); single process: {fps1:.1f} frames/s",
+        cfg_name = "C1" if args.config == "C5" else args.config
+        procs = min(cores, S)
+        fpath = dump_frames_for_cpu(m["h_frames"].numpy(), procs)
+        fps1, feats1, t1, kind = cpu_tracker_throughput(cfg_name, args.cpu_frames, 1, threads=1, use_ransac=bool(args.ransac),
+                                                        frames_path=fpath)
+        fpsN, featsN, tN, kind = cpu_tracker_throughput(cfg_name, args.cpu_frames, procs, threads=1,
+                                                        use_ransac=bool(args.ransac), frames_path=fpath)
+        os.unlink(fpath)
+        cpu = {"value": fpsN, "unit": UNIT, "cores": procs, "kind": kind,
+               "sample": f"{procs} processes x {args.cpu_frames} frames, one stream each = streams 0..{procs - 1} of this run's own "
+                         f"frames ({m['n_buf']} buffered frames walked back and forth, as the GPU arm does); {cpu_kind_text(kind)}, "
+                         f"1 thread per process; single process: {fps1:.1f} frames/s",
                "single_process_value": fps1, "features_per_s": featsN}
 
     clocks.stop()
+    link_all = m["h2d_all_sum"]
+    e2e = {"value": m["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": m["step_bytes"], "d2h_bytes_per_step": m["d2h_bytes"],
+           "ms_per_step": 1e3 * m["e2e_s"] / K, "api": "vs_tracker_submit_batch / vs_tracker_wait, two batches in flight",
+           "sync_call_value": (m["total_frames"] / m["e2e_sync_s"]) if m["e2e_sync_s"] else None,
+           "h2d_link_gbs": m["h2d_all_min"], "h2d_link_gbs_solo_per_gpu": m["h2d_solo"], "h2d_link_gbs_all_ranks_sum": link_all,
+           "host_cpus_bound": numa_cpus, "link_bound_frames_per_s": link_all * 1e9 / (H * W),
+           "frac_of_link_bound": m["e2e_value"] / (link_all * 1e9 / (H * W)),
+           "gather_ms": m["gather_ms"]}
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
-        "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8/int32/f32", "data": "synthetic",
+        "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": m["dev_ms"] / K, "higher_is_better": True, "scaling": "strong" if args.config == "C5" else "weak",
+        "vs_baseline": None, "dtype": "u8/int32/f32", "data": "synthetic",
         "config": dict(workload_config(args, cfg, S),
-                       l2=f"no flush: a step streams {S} new frames ({step_bytes / 1e6:.0f} MB) plus "
-                          f"two pyramids per stream through HBM, > 126 MB L2" if step_bytes * 3 > 126e6 else
-                          "working set below L2 size (small --streams); not a roofline run",
-                       frames_buffered=n_buf),
-        "features_per_s": value * pub_mean, "features_per_frame": pub_mean,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": step_bytes, "d2h_bytes_per_step": d2h_bytes,
-                "ms_per_step": 1e3 * e2e_s / K, "api": "vs_tracker_submit_batch / vs_tracker_wait, two batches in flight",
-                "sync_call_value": total_frames / e2e_sync_s, "h2d_link_gbs": h2d_gbs, "host_cpus_bound": numa_cpus,
-                "link_bound_frames_per_s": world * h2d_gbs * 1e9 / (H * W)},
-        "gpu_launches": int(launches),
-        "latency_us": lat,
-        "roofline": roofline,
-        "frame_hbm_frac": frame_frac, "alg_bytes_per_frame": alg["frame"],
-        "stages": stages, "kernels": kernels, "profiled_ms_per_step": step_prof_ms,
+                       l2=(f"no flush: a step streams {S} new frames ({m['step_bytes'] / 1e6:.0f} MB) plus "
+                           f"two pyramids per stream through HBM, > 126 MB L2") if m["step_bytes"] * 3 > 126e6 else
+                          "working set of one step below the 126 MB L2 (few streams per GPU): latency/launch-bound regime, not a roofline run",
+                       frames_buffered=m["n_buf"]),
+        "timed_repeats_ms": m["rep_ms"], "timed_repeat_reported": "median",
+        "features_per_s": m["value"] * m["pub_mean"], "features_per_frame": m["pub_mean"],
+        "e2e": e2e,
+        "gpu_launches": m["launches"],
+        "latency_us": m["lat"],
+        "roofline": R["roofline"],
+        "frame_hbm_frac": R["frame_hbm_frac"], "alg_bytes_per_frame": R["alg_bytes_per_frame"],
+        "stages": R["stages"], "kernels": R["kernels"], "profiled_ms_per_step": R["profiled_ms_per_step"],
         "cpu_baseline": cpu,
         "clocks": clocks.summary(),
     }
+    if m1 is not None:
+        R1 = roofline_of(m1, K, world, peak, peak_src)
+        line["c1"] = {"config": workload_config(args, m1["cfg"], m1["S"], name="C1"), "value": m1["value"],
+                      "ms_per_step": m1["dev_ms"] / K, "features_per_frame": m1["pub_mean"],
+                      "e2e": {"value": m1["e2e_value"], "h2d_bytes_per_step": m1["step_bytes"],
+                              "d2h_bytes_per_step": m1["d2h_bytes"], "ms_per_step": 1e3 * m1["e2e_s"] / K},
+                      "roofline": R1["roofline"], "frame_hbm_frac": R1["frame_hbm_frac"],
+                      "stages": {k: {"ms_per_step": v["ms_per_step"], "frac": v["frac"]} for k, v in R1["stages"].items()}}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -617,7 +796,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
+    ap.add_argument("--config", default="C2", choices=sorted(CONFIGS) + ["C5"])
     ap.add_argument("--streams", type=int, default=512, help="camera streams per GPU")
     ap.add_argument("--ransac", type=int, default=1)
     ap.add_argument("--lanes", type=int, default=4, help="pipeline lanes of the e2e (host-frame) handle")
@@ -628,12 +807,16 @@ def main():
     ap.add_argument("--cpu-frames-per-step", type=int, default=4)
     ap.add_argument("--cpu-procs", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-c1", action="store_true", help="skip the compact C1 sub-record of the default C2 line")
+    ap.add_argument("--repeats", type=int, default=5, help="timed K-step regions of the device-resident leg; the median is reported")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3          # timing rule: W >= 3
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.config == "C5" and C5_TOTAL_STREAMS % max(world, 1):
+        raise SystemExit("C5 needs a rank count that divides 64")
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:

@@ -762,8 +762,19 @@ void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bo
     if (launches) *launches += 1;
 }
 
+int select_finish_smem_bytes(int cap) { return kSortSmemKeys * 8 + kSelBins * 4 + cap * 4; }
+
+// largest dynamic shared-memory request any glue launch makes for a handle of this capacity (vs_tracker_create checks
+// it against the device's opt-in limit, so an oversized capacity fails at creation, not at the first track call)
+int glue_max_smem_bytes(int cap) {
+    int m = set_mask_smem_bytes(cap);
+    if (m < cap * 16) m = cap * 16;                 // fused / stand-alone device RANSAC
+    const int sf = select_finish_smem_bytes(cap);
+    return m > sf ? m : sf;
+}
+
 void launch_select_finish(const GlueParams& g, cudaStream_t st, int64_t* launches) {
-    const int smem = kSortSmemKeys * 8 + kSelBins * 4 + g.cap * 4;
+    const int smem = select_finish_smem_bytes(g.cap);
     ensure_dyn_smem(reinterpret_cast<const void*>(select_finish_kernel), smem);
     launch_pdl(select_finish_kernel, dim3(g.n_streams), dim3(kFinishThreads), smem, st, g);
     if (launches) *launches += 1;

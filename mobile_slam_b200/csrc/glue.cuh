@@ -87,5 +87,7 @@ void launch_set_mask(const GlueParams& g, cudaStream_t st, int64_t* launches, bo
 void launch_select_finish(const GlueParams& g, cudaStream_t st, int64_t* launches);
 void launch_undistort(const CameraDev& cam, const float2* pts, int n, float2* out, cudaStream_t st);
 int set_mask_smem_bytes(int cap);
+int select_finish_smem_bytes(int cap);
+int glue_max_smem_bytes(int cap);
 
 }  // namespace vs

@@ -284,6 +284,18 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     if (cap < cfg->max_cnt) cap = cfg->max_cnt;
     cap = round_up(cap, 32);
     if (cap > 4096) { delete t; set_error("capacity above 4096 features per stream is not supported"); return VS_ERR_CAPACITY; }
+    {
+        // the per-stream glue kernels keep a stream's whole feature set in shared memory: refuse a capacity they cannot
+        // hold here, instead of failing at the first track call with a launch error
+        int smem_optin = 0;
+        cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device);
+        const int need = glue_max_smem_bytes(cap) + 2048;      // + the kernels' static shared memory
+        if (need > smem_optin) {
+            delete t;
+            set_error("capacity %d needs %d B of shared memory per CTA, the device allows %d", cap, need, smem_optin);
+            return VS_ERR_CAPACITY;
+        }
+    }
     t->cap = cap;
     t->cfg.capacity = cap;
 
@@ -401,7 +413,8 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     point_results(t, t->d_rblock);
     VS_TRY_CREATE(cudaMallocHost(&t->h_block, 2 * t->h_block_bytes));      // two result slots (submit / wait pipelining)
     memset(t->h_block, 0, 2 * t->h_block_bytes);
-    VS_TRY_CREATE(cudaMallocHost(&t->h_time, 2 * sizeof(double) * B));
+    VS_TRY_CREATE(cudaMallocHost(&t->h_time, vs_tracker::kTimeRing * sizeof(double) * B));
+    for (int k = 0; k < vs_tracker::kTimeRing; ++k) VS_TRY_CREATE(cudaEventCreateWithFlags(&t->ev_time[k], cudaEventDisableTiming));
     VS_TRY_CREATE(cudaEventCreateWithFlags(&t->ev_fetch[0], cudaEventDisableTiming));
     VS_TRY_CREATE(cudaEventCreateWithFlags(&t->ev_fetch[1], cudaEventDisableTiming));
     VS_TRY_CREATE(cudaMallocHost(&t->h_wn, sizeof(int) * B));
@@ -465,6 +478,7 @@ void vs_tracker_destroy(vs_tracker* t) {
     t->lanes.clear();
     if (t->ev_done) cudaEventDestroy(t->ev_done);
     for (int k = 0; k < 2; ++k) if (t->ev_fetch[k]) cudaEventDestroy(t->ev_fetch[k]);
+    for (int k = 0; k < vs_tracker::kTimeRing; ++k) if (t->ev_time[k]) cudaEventDestroy(t->ev_time[k]);
     if (t->stream) cudaStreamSynchronize(t->stream);
     t->arena.release();
     if (t->d_eig) cudaFree(t->d_eig);
@@ -715,7 +729,11 @@ static int enqueue_upload(vs_tracker* t, const uint8_t* const* frames, int strid
 // one frame per stream, images resident on the device
 static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride, int64_t image_stride_bytes,
                          const double* time_s, int slot = 0) {
-    double* h_time = t->h_time + (size_t)slot * t->B;
+    // stream-ordered timestamps: slot k of the ring is rewritten only after the frame that read it has finished
+    // (calls with results_to_host = 0 return without a sync, so a fixed slot would be overwritten under a running frame)
+    const int ts = (int)(t->time_seq % vs_tracker::kTimeRing);
+    if (t->time_seq >= vs_tracker::kTimeRing) VS_CUDA_TRY(cudaEventSynchronize(t->ev_time[ts]));
+    double* h_time = t->h_time + (size_t)ts * t->B;
     memcpy(h_time, time_s, sizeof(double) * t->B);
     static const int pdl_max = [] { const char* e = getenv("VS_PDL_MAX_STREAMS"); return e ? atoi(e) : kPdlMaxStreams; }();
     tl_pdl_launch = t->B <= pdl_max;              // programmatic dependent launches for latency-sized handles only
@@ -739,6 +757,8 @@ static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride,
     if (direct_results(t)) point_results(t, t->d_rblock);      // stage entry points and fetches use the device block
     if (rc != VS_OK) return rc;
     VS_CUDA_TRY(cudaEventRecord(t->ev1, t->stream));
+    VS_CUDA_TRY(cudaEventRecord(t->ev_time[ts], t->stream));
+    ++t->time_seq;
     prof_end(t);
     return VS_OK;
 }

@@ -74,7 +74,12 @@ struct vs_tracker {
     uint8_t* h_block = nullptr;   // results: hdr | ids | cnt | pts | un | vel
     size_t h_block_bytes = 0;
     uint8_t* d_rblock = nullptr;
+    // timestamps are read in place from pinned host memory by select_finish: a ring of slots, each guarded by an event
+    // recorded after the frame that reads it, so back-to-back unsynchronised calls never overwrite a slot still in use
+    static constexpr int kTimeRing = 8;
     double* h_time = nullptr;
+    cudaEvent_t ev_time[kTimeRing] = {};
+    int64_t time_seq = 0;
     // RANSAC callback hop
     vs_reject_fn reject_fn = nullptr;
     void* reject_user = nullptr;

@@ -60,8 +60,8 @@ __device__ __forceinline__ void pdl_entry() {
 // Opt a kernel in to more than 48 KB of dynamic shared memory.  The attribute is per device, and one process may
 // drive several GPUs (vs::ShardedTracker: one thread + handle per GPU), so what was set is remembered per
 // (kernel, device).
-inline void ensure_dyn_smem(const void* kernel, int bytes) {
-    if (bytes <= 48 * 1024) return;
+inline cudaError_t ensure_dyn_smem(const void* kernel, int bytes) {
+    if (bytes <= 48 * 1024) return cudaSuccess;
     static std::mutex mu;
     static std::map<std::pair<const void*, int>, int> done;
     int dev = 0;
@@ -69,9 +69,11 @@ inline void ensure_dyn_smem(const void* kernel, int bytes) {
     std::lock_guard<std::mutex> lock(mu);
     int& have = done[std::make_pair(kernel, dev)];
     if (have < bytes) {
-        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e != cudaSuccess) return e;          // the following launch fails too and cudaGetLastError reports it
         have = bytes;
     }
+    return cudaSuccess;
 }
 
 // Set by the frame enqueue per handle: on for few-stream (latency) handles.  For big stream batches the kernels are

@@ -30,31 +30,39 @@ _ROW = 9
 
 
 def pack_tracks(stream_ids, results) -> np.ndarray:
-    """(sum n_s, 9) float64 rows [stream, id, track_cnt, u, v, x, y, vx, vy] of the given StreamResults."""
+    """(n_streams + sum n_s, 9) float64: per stream one header row [stream, -1, -1, n_s, 0...] (track_cnt is never
+    negative, so -1 marks it) followed by n_s rows [stream, id, track_cnt, u, v, x, y, vx, vy].  The header keeps a
+    stream that currently has no features (featureless frame, scene cut) present in the gathered result."""
     rows = []
     for sid, r in zip(stream_ids, results):
         n = len(r.ids)
-        a = np.empty((n, _ROW), np.float64)
+        a = np.zeros((n + 1, _ROW), np.float64)
         a[:, 0] = sid
-        a[:, 1] = r.ids
-        a[:, 2] = r.track_cnt
-        a[:, 3:5] = r.cur_pts
-        a[:, 5:7] = r.cur_undistorted_pts
-        a[:, 7:9] = r.pts_velocity
+        a[0, 1:4] = (-1, -1, n)
+        a[1:, 1] = r.ids
+        a[1:, 2] = r.track_cnt
+        a[1:, 3:5] = r.cur_pts
+        a[1:, 5:7] = r.cur_undistorted_pts
+        a[1:, 7:9] = r.pts_velocity
         rows.append(a)
     return np.concatenate(rows) if rows else np.zeros((0, _ROW), np.float64)
 
 
 def unpack_tracks(packed: np.ndarray) -> dict:
-    """{stream: dict(ids, track_cnt, cur_pts, cur_undistorted_pts, pts_velocity)} in stream order."""
+    """{stream: dict(ids, track_cnt, cur_pts, cur_undistorted_pts, pts_velocity)} for every packed stream, streams
+    without features included (empty arrays), in ascending stream order."""
     out = {}
-    sids = packed[:, 0].astype(np.int64)
-    for sid in np.unique(sids):
-        a = packed[sids == sid]
-        out[int(sid)] = dict(ids=a[:, 1].astype(np.int32), track_cnt=a[:, 2].astype(np.int32),
-                             cur_pts=a[:, 3:5].astype(np.float32), cur_undistorted_pts=a[:, 5:7].astype(np.float32),
-                             pts_velocity=a[:, 7:9].astype(np.float32))
-    return out
+    i, n_rows = 0, packed.shape[0]
+    while i < n_rows:
+        if packed[i, 2] != -1:
+            raise ValueError("unpack_tracks: missing stream header row")
+        sid, n = int(packed[i, 0]), int(packed[i, 3])
+        a = packed[i + 1:i + 1 + n]
+        out[sid] = dict(ids=a[:, 1].astype(np.int32), track_cnt=a[:, 2].astype(np.int32),
+                        cur_pts=a[:, 3:5].astype(np.float32), cur_undistorted_pts=a[:, 5:7].astype(np.float32),
+                        pts_velocity=a[:, 7:9].astype(np.float32))
+        i += 1 + n
+    return dict(sorted(out.items()))
 
 
 def gather_tracks(stream_ids, results, dst: int = 0):

@@ -316,3 +316,30 @@ def test_ragged_batch_blank_and_busy_streams_together(built_lib):
     batch.close()
     for t in singles:
         t.close()
+
+
+def test_unsynchronised_device_calls_keep_their_timestamps(built_lib):
+    """vs_tracker_track_batch_device(results_to_host = 0) returns without a sync; back-to-back calls must still see
+    their OWN timestamps (stream-ordered timestamp ring), i.e. velocities equal the synchronous path's."""
+    torch = pytest.importorskip("torch")
+    cfg = dict(CONFIGS["C2"], width=376, height=240, max_cnt=100, min_dist=15, intr=(230.0, 230.0, 188.0, 120.0))
+    n_streams, n_frames = 3, 14               # more frames than ring slots
+    W, H = cfg["width"], cfg["height"]
+    streams = [SynthStream(60 + s, W, H, motion=1.5) for s in range(n_streams)]
+    frames = np.stack([np.stack([s.frame(k) for s in streams]) for k in range(n_frames)])     # (k, s, H, W)
+    times = [[0.05 * k + 0.011 * s * k for s in range(n_streams)] for k in range(n_frames)]   # uneven dt per stream
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    d = torch.from_numpy(frames).cuda()
+    sync = BatchTracker(tc, cam, n_streams)
+    want = [sync.track_device(d[k].data_ptr(), W, H * W, times[k], to_host=True) for k in range(n_frames)]
+    sync.close()
+    fast = BatchTracker(tc, cam, n_streams)
+    for k in range(n_frames):
+        fast.track_device(d[k].data_ptr(), W, H * W, times[k], to_host=False)
+    got = fast.fetch()
+    for s in range(n_streams):
+        assert np.array_equal(got[s].ids, want[-1][s].ids)
+        assert np.array_equal(got[s].cur_pts, want[-1][s].cur_pts)
+        assert np.array_equal(got[s].pts_velocity, want[-1][s].pts_velocity)
+        assert np.any(got[s].pts_velocity != 0.0)
+    fast.close()

@@ -43,6 +43,11 @@ def test_pack_unpack_roundtrip_single_process():
         assert np.array_equal(out[s]["ids"], r.ids) and np.array_equal(out[s]["track_cnt"], r.track_cnt)
         assert np.array_equal(out[s]["cur_pts"], r.cur_pts) and np.array_equal(out[s]["pts_velocity"], r.pts_velocity)
     assert sharding.gather_tracks([], []) == {}
+    # a stream without features stays in the gathered result (empty arrays), in stream order
+    empty = StreamResult(ids=np.zeros(0, np.int32), track_cnt=np.zeros(0, np.int32), cur_pts=np.zeros((0, 2), np.float32),
+                         cur_undistorted_pts=np.zeros((0, 2), np.float32), pts_velocity=np.zeros((0, 2), np.float32), n_new=0)
+    out = sharding.gather_tracks([4, 2, 7], [_fake_result(4, 0), empty, _fake_result(7, 0)])
+    assert list(out) == [2, 4, 7] and len(out[2]["ids"]) == 0 and out[2]["cur_pts"].shape == (0, 2)
     assert sharding.max_over_ranks(1.5) == 1.5
 
 

@@ -20,10 +20,13 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 #include <fstream>
+#include <condition_variable>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <sstream>
 #include <stdexcept>
 #include <string>
@@ -68,6 +71,7 @@ struct FrontendConfig {
     int equalize = 1, fisheye = 0;
     int lk_window_size = 21, lk_pyramid_levels = 3, lk_iterations = 30;
     double lk_eps = 0.01;
+    std::string fisheye_mask;             // g_config.feature_tracker.fisheye_mask: mask image file (feature_tracker.cpp:42-46)
     int device = 0;
 #ifdef VS_WITH_OPENCV
     int ransac_mode = VS_RANSAC_CALLBACK;
@@ -243,7 +247,7 @@ public:
 private:
     static size_t row_bytes(const Image& img) {
 #ifdef VS_WITH_OPENCV
-        return img.step[0];
+        return (size_t)img.step;
 #else
         return img.step;
 #endif
@@ -258,14 +262,47 @@ private:
         c.equalize = g.feature_tracker.equalize; c.fisheye = g.feature_tracker.fisheye;
         c.lk_window_size = g.feature_tracker.lk_window_size; c.lk_pyramid_levels = g.feature_tracker.lk_pyramid_levels;
         c.lk_iterations = g.feature_tracker.lk_iterations; c.lk_eps = g.feature_tracker.lk_eps;
+        c.fisheye_mask = g.feature_tracker.fisheye_mask;
 #endif
         return c;
     }
     void reset_handle() { if (handle_) { vs_tracker_destroy(handle_); handle_ = nullptr; } }
+    // feature_tracker.cpp:42-46: the mask file is read once, lazily, the first time a frame is tracked with `fisheye` set;
+    // an unreadable or wrongly sized file falls back to the generated circle (there: `fisheye_mask.empty()`)
+    bool load_mask_image(const vs::FrontendConfig& c, int cols, int rows, std::vector<uint8_t>* out) {
+        out->clear();
+        if (!c.fisheye || c.fisheye_mask.empty()) return false;
+#ifdef VS_WITH_OPENCV
+        cv::Mat m = cv::imread(c.fisheye_mask, cv::IMREAD_GRAYSCALE);
+        if (m.empty() || m.cols != cols || m.rows != rows) return false;
+        out->resize((size_t)cols * rows);
+        for (int y = 0; y < rows; ++y) std::memcpy(out->data() + (size_t)y * cols, m.ptr<uint8_t>(y), (size_t)cols);
+        return true;
+#else
+        int32_t w = 0, h = 0;
+        out->resize((size_t)cols * rows);
+        if (vs_image_read_gray(c.fisheye_mask.c_str(), out->data(), cols, cols, rows, &w, &h) != VS_OK || w != cols || h != rows) {
+            out->clear();
+            return false;
+        }
+        return true;
+#endif
+    }
     void ensure_handle(int cols, int rows) {
-        if (handle_) return;
-        if (!have_camera_) throw std::runtime_error("FeatureTracker: camera intrinsics not set");
         const vs::FrontendConfig c = current();
+        // the reference takes inBorder limits, mask size and the virtual-pinhole centre from g_config.camera.row/col and
+        // everything else from the image; its callers always hand over rowRange(0, camera.row) of a camera.col-wide image
+        // (measurement_processor.cpp:191), and OpenCV throws in calcOpticalFlowPyrLK when the size changes mid-run
+        if (c.col != cols || c.row != rows)
+            throw std::runtime_error("FeatureTracker: image is " + std::to_string(cols) + "x" + std::to_string(rows) +
+                                     " but camera.col x camera.row is " + std::to_string(c.col) + "x" + std::to_string(c.row));
+        if (handle_) {
+            if (cols != handle_cols_ || rows != handle_rows_)
+                throw std::runtime_error("FeatureTracker: image size changed from " + std::to_string(handle_cols_) + "x" +
+                                         std::to_string(handle_rows_) + " to " + std::to_string(cols) + "x" + std::to_string(rows));
+            return;
+        }
+        if (!have_camera_) throw std::runtime_error("FeatureTracker: camera intrinsics not set");
         vs_tracker_config tc;
         vs_tracker_default_config(&tc);
         tc.device = c.device;
@@ -280,13 +317,18 @@ private:
         tc.ransac_mode = c.ransac_mode;
         tc.capacity = c.max_cnt > 1024 ? c.max_cnt : 1024;    // room for setMobileParams to raise max_cnt later
         tc.camera = camera_;
+        std::vector<uint8_t> mask;
+        if (load_mask_image(c, cols, rows, &mask)) { tc.fisheye_mask_image = mask.data(); tc.fisheye_mask_stride = cols; mask_loaded_ = true; }
         vs::check(vs_tracker_create(&tc, nullptr, &handle_));
+        handle_cols_ = cols; handle_rows_ = rows;
         applied_ = c;
 #ifdef VS_WITH_OPENCV
         if (c.ransac_mode == VS_RANSAC_CALLBACK) vs::check(vs_tracker_set_reject_callback(handle_, &FeatureTracker::reject_cv, this));
 #endif
     }
-    // VIOEngine::setMobileParams / setFThreshold / setTrackingParams mutate g_config between frames (vio_engine.cpp:354-389)
+    // Every call re-reads the configuration like the reference does (g_config is read inside detectAndTrack / setMask /
+    // rejectWithFundamentalMatrix): the VIOEngine mutators (vio_engine.cpp:354-389) and direct writes to equalize,
+    // fisheye and camera.focal_length all take effect on the next frame without losing the tracking state.
     void apply_runtime_params() {
         const vs::FrontendConfig c = current();
         if (c.max_cnt != applied_.max_cnt || c.min_dist != applied_.min_dist || c.f_threshold != applied_.f_threshold ||
@@ -295,8 +337,27 @@ private:
             c.f_threshold_edge_factor != applied_.f_threshold_edge_factor) {
             vs::check(vs_tracker_set_params(handle_, c.max_cnt, c.min_dist, c.f_threshold, c.lk_window_size, c.lk_pyramid_levels,
                                             c.lk_iterations, c.lk_eps, c.f_threshold_edge_factor));
-            applied_ = c;
+            // vs_tracker_set_params keeps the guards of VIOEngine::setTrackingParams (values <= 0, even windows and
+            // levels > 5 leave the field unchanged): say so when a value written straight into the config was not taken
+            vs_tracker_config eff;
+            vs::check(vs_tracker_get_config(handle_, &eff));
+            auto warn = [](const char* name, double want, double have) {
+                if (want != have) std::fprintf(stderr, "[vs] %s = %g is not supported at run time, the tracker keeps %g\n", name, want, have);
+            };
+            warn("max_cnt", c.max_cnt, eff.max_cnt); warn("min_dist", c.min_dist, eff.min_dist);
+            warn("f_threshold", c.f_threshold, eff.f_threshold); warn("lk_window_size", c.lk_window_size, eff.lk_window_size);
+            warn("lk_pyramid_levels", c.lk_pyramid_levels, eff.lk_pyramid_levels);
+            warn("lk_iterations", c.lk_iterations, eff.lk_iterations); warn("lk_eps", c.lk_eps, eff.lk_eps);
+            warn("f_threshold_edge_factor", c.f_threshold_edge_factor, eff.f_threshold_edge_factor);
         }
+        if (c.equalize != applied_.equalize || c.fisheye != applied_.fisheye || c.focal_length != applied_.focal_length) {
+            std::vector<uint8_t> mask;
+            const bool first_fisheye = c.fisheye && !applied_.fisheye && !mask_loaded_ && load_mask_image(c, handle_cols_, handle_rows_, &mask);
+            vs::check(vs_tracker_set_frontend_flags(handle_, c.equalize ? 1 : 0, c.fisheye ? 1 : 0, c.focal_length,
+                                                    first_fisheye ? mask.data() : nullptr, handle_cols_));
+            if (first_fisheye) mask_loaded_ = true;
+        }
+        applied_ = c;
     }
 #ifdef VS_WITH_OPENCV
     // rejectWithFundamentalMatrix, feature_tracker.cpp:226-299: the lift to the virtual pinhole was done on the GPU,
@@ -305,22 +366,29 @@ private:
         auto* self = static_cast<FeatureTracker*>(user);
         const vs::FrontendConfig c = self->current();
         std::vector<cv::Point2f> A(n), B(n);
-        for (int i = 0; i < n; ++i) { A[i] = {a[2 * i], a[2 * i + 1]}; B[i] = {b[2 * i], b[2 * i + 1]}; }
+        for (int i = 0; i < n; ++i) { A[i] = cv::Point2f(a[2 * i], a[2 * i + 1]); B[i] = cv::Point2f(b[2 * i], b[2 * i + 1]); }
         std::vector<uchar> st;
         cv::Mat F = cv::findFundamentalMat(A, B, cv::FM_RANSAC, c.f_threshold, 0.99, st);
         for (int i = 0; i < n; ++i) status[i] = i < (int)st.size() ? st[i] : 0;
-        if (c.f_threshold_edge_factor > 0.0 && !F.empty() && F.rows == 3) {
-            const double cx = c.col / 2.0, cy = c.row / 2.0, rmax = std::sqrt(cx * cx + cy * cy);
-            cv::Mat Fd; F.convertTo(Fd, CV_64F);
+        const double edge_factor = c.f_threshold_edge_factor;
+        if (edge_factor > 0.0 && !F.empty() && F.rows == 3 && F.cols == 3) {          // feature_tracker.cpp:236-285
+            const double cx = c.col / 2.0, cy = c.row / 2.0;
+            const double r_max = std::sqrt(cx * cx + cy * cy);
+            const double r_max_inv = (r_max > 1e-6) ? 1.0 / r_max : 0.0;
+            const double* f = F.ptr<double>();
             for (int i = 0; i < n; ++i) {
                 if (status[i]) continue;
-                const double dx = px[2 * i] - cx, dy = px[2 * i + 1] - cy, rr = std::sqrt(dx * dx + dy * dy) / rmax;
-                if (rr < 0.3) continue;
-                const double thr = c.f_threshold * (1.0 + c.f_threshold_edge_factor * rr * rr);
-                const cv::Mat x1 = (cv::Mat_<double>(3, 1) << A[i].x, A[i].y, 1.0), x2 = (cv::Mat_<double>(3, 1) << B[i].x, B[i].y, 1.0);
-                const cv::Mat l = Fd * x1;
-                const double num = std::abs(x2.dot(l)), den = std::sqrt(l.at<double>(0) * l.at<double>(0) + l.at<double>(1) * l.at<double>(1));
-                if (den > 1e-10 && num / den < thr) status[i] = 1;
+                const double dx = px[2 * i] - cx, dy = px[2 * i + 1] - cy;
+                const double r_ratio = std::sqrt(dx * dx + dy * dy) * r_max_inv;
+                if (r_ratio < 0.3) continue;
+                const double u1 = A[i].x, v1 = A[i].y, u2 = B[i].x, v2 = B[i].y;
+                const double la = f[0] * u1 + f[1] * v1 + f[2];
+                const double lb = f[3] * u1 + f[4] * v1 + f[5];
+                const double lc = f[6] * u1 + f[7] * v1 + f[8];
+                const double norm_ab = std::sqrt(la * la + lb * lb);
+                if (norm_ab < 1e-12) continue;
+                const double dist = std::abs(la * u2 + lb * v2 + lc) / norm_ab;
+                if (dist < c.f_threshold * (1.0 + edge_factor * r_ratio * r_ratio)) status[i] = 1;
             }
         }
         return 0;
@@ -329,6 +397,8 @@ private:
     vs_tracker* handle_ = nullptr;
     vs_camera camera_{};
     bool have_camera_ = false;
+    bool mask_loaded_ = false;
+    int handle_cols_ = 0, handle_rows_ = 0;
     vs::FrontendConfig applied_{};
     std::vector<int> real_ids_;
 };
@@ -337,64 +407,197 @@ private:
 
 namespace vs {
 
-// Stream-sharded multi-GPU host layer: stream s lives on GPU s mod G, one host thread + one handle
-// (one CUDA context / stream set) per GPU, no collective — only this host-side gather of the per-stream results.
+// ---- the callers' side of the path -------------------------------------------------------------
+// What MeasurementProcessor::extractImageFeatures (src/utility/measurement_processor.cpp:178-231) returns for one frame:
+// rays (id, x, y, 1) plus the five channels id, u, v, vx, vy of every feature with track_cnt > 1 (ImageFeatureMsg).
+struct ImageFeatureMsg {
+    double timestamp = 0.0;
+    std::string frame_id;
+    int points_count = 0;
+    int channels_count = 0;
+    struct Point3D { int id; double x, y, z; };
+    std::vector<Point3D> ray_vectors;
+    std::vector<double> channel_data[5];       // id, u, v, velocity_x, velocity_y
+};
+
+// the publish loop shared by both callers (measurement_processor.cpp:200-231, vio_engine.cpp:219-239)
+inline void publish(const frontend::FeatureTracker& ft, ImageFeatureMsg* msg) {
+    for (size_t j = 0; j < ft.ids.size(); ++j) {
+        if (ft.track_cnt[j] <= 1) continue;
+        const int id = ft.ids[j];
+        msg->ray_vectors.push_back({id, ft.cur_undistorted_pts[j].x, ft.cur_undistorted_pts[j].y, 1.0});
+        msg->channel_data[0].push_back(id);
+        msg->channel_data[1].push_back(ft.cur_pts[j].x);
+        msg->channel_data[2].push_back(ft.cur_pts[j].y);
+        msg->channel_data[3].push_back(ft.pts_velocity[j].x);
+        msg->channel_data[4].push_back(ft.pts_velocity[j].y);
+    }
+    msg->points_count = (int)msg->ray_vectors.size();
+    msg->channels_count = 5;
+}
+
+// MeasurementProcessor::extractImageFeatures: read the file as grey (cv::imread(path, IMREAD_GRAYSCALE) with OpenCV, the
+// library's own PNG / PGM decoder without), track rowRange(0, camera.row), run the updateID loop, publish.  An unreadable
+// file returns the message with only timestamp and frame_id set, like the reference ("Cannot load image").
+inline ImageFeatureMsg extractImageFeatures(frontend::FeatureTracker& ft, const std::string& full_path, const std::string& filename,
+                                            double timestamp, int camera_row, int camera_col) {
+    ImageFeatureMsg msg;
+    msg.timestamp = timestamp;
+    msg.frame_id = filename;
+#ifdef VS_WITH_OPENCV
+    cv::Mat show_img = cv::imread(full_path, cv::IMREAD_GRAYSCALE);
+    if (show_img.empty()) { std::fprintf(stderr, "Cannot load image: %s\n", full_path.c_str()); return msg; }
+    ft.detectAndTrack(show_img.rowRange(0, camera_row), timestamp);
+    (void)camera_col;
+#else
+    std::vector<uint8_t> buf((size_t)camera_row * camera_col);
+    int32_t w = 0, h = 0;
+    if (vs_image_read_gray(full_path.c_str(), buf.data(), camera_col, camera_col, camera_row, &w, &h) != VS_OK || w != camera_col || h < camera_row) {
+        std::fprintf(stderr, "Cannot load image: %s (%s)\n", full_path.c_str(), vs_last_error());
+        return msg;
+    }
+    ft.detectAndTrack(frontend::FeatureTracker::Image(buf.data(), camera_col, camera_row), timestamp);
+#endif
+    for (unsigned int i = 0;; i++)
+        if (!ft.updateID(i)) break;
+    publish(ft, &msg);
+    return msg;
+}
+
+// The front-end half of VIOEngine::processFrame (src/vio_engine.cpp:180, 210-239): wrap the caller's grey buffer without
+// copying, track, run the updateID loop and build common::ImageData (id -> [x, y, 1, u, v, vx, vy]).
+inline std::map<int, std::vector<double>> processFrameFrontend(frontend::FeatureTracker& ft, const uint8_t* gray_image, int width,
+                                                               int height, double image_timestamp) {
+#ifdef VS_WITH_OPENCV
+    cv::Mat img(height, width, CV_8UC1, const_cast<uint8_t*>(gray_image));
+#else
+    frontend::FeatureTracker::Image img(gray_image, width, height);
+#endif
+    ft.detectAndTrack(img, image_timestamp);
+    for (unsigned int i = 0;; i++)
+        if (!ft.updateID(i)) break;
+    return ft.imageData();
+}
+
+// Stream-sharded multi-GPU host layer: stream s lives on GPU s mod G, one handle (one CUDA context /
+// stream set) and ONE PERSISTENT WORKER THREAD per GPU, no collective — only the host-side gather of the per-stream
+// results.  submit() / wait() map onto vs_tracker_submit_batch / vs_tracker_wait of every shard (two batches may be in
+// flight, so the upload of batch k+1 overlaps the kernels of batch k on every GPU); track() = submit() + wait().
 class ShardedTracker {
 public:
     ShardedTracker(const vs_tracker_config& base, int n_streams, int n_gpus, int lanes_per_gpu = 4) : n_streams_(n_streams) {
         if (n_gpus < 1 || n_streams < n_gpus) throw std::runtime_error("ShardedTracker: need 1 <= n_gpus <= n_streams");
-        shards_.resize(n_gpus);
+        for (int g = 0; g < n_gpus; ++g) shards_.emplace_back(new Shard());
         for (int g = 0; g < n_gpus; ++g) {
-            for (int s = g; s < n_streams; s += n_gpus) shards_[g].streams.push_back(s);
+            Shard& sh = *shards_[g];
+            for (int s = g; s < n_streams; s += n_gpus) sh.streams.push_back(s);
             vs_tracker_config c = base;
             c.device = g;
-            c.n_streams = (int)shards_[g].streams.size();
+            c.n_streams = (int)sh.streams.size();
             c.pipeline_lanes = lanes_per_gpu;
-            check(vs_tracker_create(&c, nullptr, &shards_[g].handle));
-            shards_[g].res.resize(c.n_streams);
-            shards_[g].frames.resize(c.n_streams);
-            shards_[g].times.resize(c.n_streams);
+            const int rc = vs_tracker_create(&c, nullptr, &sh.handle);
+            if (rc != VS_OK) { const Error e(rc, vs_last_error()); shutdown(); throw e; }
+            sh.res.resize(c.n_streams);
+            for (int k = 0; k < 2; ++k) { sh.frames[k].resize(c.n_streams); sh.times[k].resize(c.n_streams); }
         }
+        for (auto& sp : shards_) { Shard* sh = sp.get(); sh->worker = std::thread([this, sh] { worker_loop(*sh); }); }
         results_.resize(n_streams);
     }
-    ~ShardedTracker() { for (auto& s : shards_) if (s.handle) vs_tracker_destroy(s.handle); }
+    ~ShardedTracker() { shutdown(); }
     ShardedTracker(const ShardedTracker&) = delete;
     ShardedTracker& operator=(const ShardedTracker&) = delete;
 
-    // frames[s]: H x stride host image of stream s; returns results indexed by global stream id (valid until next call)
-    const std::vector<vs_track_result>& track(const uint8_t* const* frames, int stride, const double* time_s) {
-        std::vector<std::thread> th;
-        std::vector<int> rc(shards_.size(), 0);
-        std::vector<std::string> err(shards_.size());
-        for (size_t g = 0; g < shards_.size(); ++g) {
-            th.emplace_back([&, g] {
-                Shard& sh = shards_[g];
-                for (size_t k = 0; k < sh.streams.size(); ++k) { sh.frames[k] = frames[sh.streams[k]]; sh.times[k] = time_s[sh.streams[k]]; }
-                rc[g] = vs_tracker_track_batch(sh.handle, sh.frames.data(), stride, sh.times.data(), sh.res.data());
-                if (rc[g] != VS_OK) err[g] = vs_last_error();          // vs_last_error is thread local
-            });
+    // frames[s]: H x stride host image of stream s; must stay valid until the matching wait() returns
+    void submit(const uint8_t* const* frames, int stride, const double* time_s) {
+        if (submitted_ - waited_ >= 2) throw std::runtime_error("ShardedTracker: two batches already in flight, call wait()");
+        const int slot = (int)(submitted_ & 1);
+        for (auto& sp : shards_) {
+            Shard& sh = *sp;
+            for (size_t k = 0; k < sh.streams.size(); ++k) { sh.frames[slot][k] = frames[sh.streams[k]]; sh.times[slot][k] = time_s[sh.streams[k]]; }
+            post(sh, slot, stride, kSubmit);
         }
-        for (auto& t : th) t.join();
-        for (size_t g = 0; g < shards_.size(); ++g) {
-            if (rc[g] != VS_OK) throw Error(rc[g], err[g].c_str());
-            for (size_t k = 0; k < shards_[g].streams.size(); ++k) results_[shards_[g].streams[k]] = shards_[g].res[k];   // host gather
-        }
+        join_all();
+        ++submitted_;
+    }
+    // results of the OLDEST submitted batch, indexed by global stream id (valid until the second wait() after this one)
+    const std::vector<vs_track_result>& wait() {
+        if (submitted_ == waited_) throw std::runtime_error("ShardedTracker: nothing in flight");
+        for (auto& sp : shards_) post(*sp, 0, 0, kWait);
+        join_all();
+        ++waited_;
+        for (auto& sp : shards_)
+            for (size_t k = 0; k < sp->streams.size(); ++k) results_[sp->streams[k]] = sp->res[k];       // the host-side gather
         return results_;
+    }
+    const std::vector<vs_track_result>& track(const uint8_t* const* frames, int stride, const double* time_s) {
+        submit(frames, stride, time_s);
+        return wait();
     }
     int n_gpus() const { return (int)shards_.size(); }
     int n_streams() const { return n_streams_; }
 
 private:
+    enum Cmd { kIdle = 0, kSubmit, kWait, kQuit };
     struct Shard {
         vs_tracker* handle = nullptr;
         std::vector<int> streams;
         std::vector<vs_track_result> res;
-        std::vector<const uint8_t*> frames;
-        std::vector<double> times;
+        std::vector<const uint8_t*> frames[2];
+        std::vector<double> times[2];
+        std::thread worker;
+        std::mutex mu;
+        std::condition_variable cv;
+        int cmd = kIdle, slot = 0, stride = 0;
+        bool done = true;
+        int rc = VS_OK;
+        std::string err;
     };
-    std::vector<Shard> shards_;
+    void post(Shard& sh, int slot, int stride, int cmd) {
+        std::lock_guard<std::mutex> lk(sh.mu);
+        sh.cmd = cmd; sh.slot = slot; sh.stride = stride; sh.done = false;
+        sh.cv.notify_all();
+    }
+    void join_all() {
+        int rc = VS_OK;
+        std::string err;
+        for (auto& sp : shards_) {
+            Shard& sh = *sp;
+            std::unique_lock<std::mutex> lk(sh.mu);
+            sh.cv.wait(lk, [&] { return sh.done; });
+            if (sh.rc != VS_OK && rc == VS_OK) { rc = sh.rc; err = sh.err; }
+        }
+        if (rc != VS_OK) throw Error(rc, err.c_str());
+    }
+    void worker_loop(Shard& sh) {
+        for (;;) {
+            int cmd, slot, stride;
+            {
+                std::unique_lock<std::mutex> lk(sh.mu);
+                sh.cv.wait(lk, [&] { return sh.cmd != kIdle; });
+                cmd = sh.cmd; slot = sh.slot; stride = sh.stride;
+                sh.cmd = kIdle;
+            }
+            if (cmd == kQuit) return;
+            int rc = cmd == kSubmit ? vs_tracker_submit_batch(sh.handle, sh.frames[slot].data(), stride, sh.times[slot].data())
+                                    : vs_tracker_wait(sh.handle, sh.res.data());
+            std::lock_guard<std::mutex> lk(sh.mu);
+            sh.rc = rc;
+            if (rc != VS_OK) sh.err = vs_last_error();          // vs_last_error is thread local
+            sh.done = true;
+            sh.cv.notify_all();
+        }
+    }
+    void shutdown() {
+        for (auto& sp : shards_) {
+            Shard& sh = *sp;
+            if (sh.worker.joinable()) { post(sh, 0, 0, kQuit); sh.worker.join(); }
+            if (sh.handle) { vs_tracker_destroy(sh.handle); sh.handle = nullptr; }
+        }
+    }
+    std::vector<std::unique_ptr<Shard>> shards_;      // Shard holds a mutex: not movable
     std::vector<vs_track_result> results_;
     int n_streams_;
+    int64_t submitted_ = 0, waited_ = 0;
 };
 
 }  // namespace vs

@@ -156,6 +156,12 @@ VS_API int vs_tracker_fetch_results(struct vs_tracker* t, vs_track_result* out /
 VS_API int vs_tracker_set_params(struct vs_tracker* t, int32_t max_cnt, int32_t min_dist, double f_threshold,
                           int32_t lk_window, int32_t lk_pyramid, int32_t lk_iterations, double lk_eps,
                           double f_edge_factor);
+/* The remaining g_config fields the reference re-reads on every call (feature_tracker.cpp:39-46,52-55,102,214-222):
+ * equalize (CLAHE on/off), fisheye (mask on/off; the mask = fisheye_mask_image if given, else the auto circle) and
+ * camera.focal_length.  Negative equalize / fisheye, focal_length <= 0 and a NULL image leave that field unchanged.
+ * Tracking state is kept.  Not valid while a submitted batch is in flight. */
+VS_API int vs_tracker_set_frontend_flags(struct vs_tracker* t, int32_t equalize, int32_t fisheye, double focal_length,
+                                         const uint8_t* fisheye_mask_image, int32_t fisheye_mask_stride);
 VS_API int vs_tracker_set_reject_callback(struct vs_tracker* t, vs_reject_fn fn, void* user);
 VS_API int vs_tracker_reset(struct vs_tracker* t, int32_t stream /* -1 = all */);
 /* number of CUDA kernels this handle has launched so far (bench.py "gpu_launches") */
@@ -197,6 +203,36 @@ VS_API int vs_tracker_set_profiling(struct vs_tracker* t, int32_t on);
  * (x = undist.x, y = undist.y, 1, u = cur_pts.x, v = cur_pts.y, vx, vy).  Host-side, needs no GPU.  *n_out = records
  * written; VS_ERR_CAPACITY if max_n is too small (nothing beyond max_n is written). */
 VS_API int vs_pack_image_features(const vs_track_result* r, int32_t max_n, int32_t* ids_out, double* rec_out, int32_t* n_out);
+
+/* A copy of the handle's current configuration (after vs_tracker_set_params / vs_tracker_set_frontend_flags);
+ * fisheye_mask_image is always NULL in the copy. */
+VS_API int vs_tracker_get_config(const struct vs_tracker* t, vs_tracker_config* out);
+
+/* ---- frame ingest: the step before the path -------------------------------------------------------------------
+ * MeasurementProcessor::extractImageFeatures (src/utility/measurement_processor.cpp:178-231) reads every frame with
+ * cv::imread(path, IMREAD_GRAYSCALE), tracks rowRange(0, g_config.camera.row) of it, runs the updateID loop and publishes
+ * the track_cnt > 1 features; VIOEngine::processFrame (src/vio_engine.cpp:180) wraps a raw grey pointer that is only
+ * valid during the call.  Host-side (no GPU needed for the two decode functions). */
+/* PNG (all colour types / bit depths, non-interlaced) or binary PGM -> 8-bit grey exactly as cv::imread(IMREAD_GRAYSCALE)
+ * returns it.  Writes min(image height, max_h) rows of out_stride bytes; *w, *h = the file's own size.  VS_ERR_INVALID
+ * ("Cannot load image: ...") for unreadable / unsupported / wider-than-max_w files. */
+VS_API int vs_image_decode_gray(const uint8_t* file_bytes, int64_t n_bytes, uint8_t* out, int32_t out_stride,
+                                int32_t max_w, int32_t max_h, int32_t* w, int32_t* h);
+VS_API int vs_image_read_gray(const char* path, uint8_t* out, int32_t out_stride, int32_t max_w, int32_t max_h,
+                              int32_t* w, int32_t* h);
+/* Pipeline around one handle: decode threads fill a ring of three pinned host slots, one coordinator thread drives
+ * vs_tracker_submit_batch / vs_tracker_wait, so batch k+2 is decoded while batch k+1 uploads and batch k is in the
+ * kernels.  submit_* return at once (VS_ERR_STATE when three batches are outstanding); vs_ingest_wait blocks for the
+ * OLDEST batch and describes it in out[n_streams] (arrays owned by the pipeline, valid until the next vs_ingest_wait).
+ * A file that cannot be decoded fails its batch's wait with VS_ERR_INVALID and the file name in vs_last_error().
+ * While a pipeline exists the handle must not be used directly.  Not available with VS_RANSAC_CALLBACK. */
+struct vs_ingest;
+typedef struct vs_ingest vs_ingest;
+VS_API int vs_ingest_create(struct vs_tracker* t, int32_t decode_threads, struct vs_ingest** out);
+VS_API int vs_ingest_submit_files(struct vs_ingest* g, const char* const* paths /* [n_streams] */, const double* time_s);
+VS_API int vs_ingest_submit_raw(struct vs_ingest* g, const uint8_t* const* frames, int32_t stride, const double* time_s);
+VS_API int vs_ingest_wait(struct vs_ingest* g, vs_track_result* out /* [n_streams] */);
+VS_API void vs_ingest_destroy(struct vs_ingest* g);
 
 /* total_ms[i] / launches[i] for kernel slot i < *n_out <= max_n; names from vs_profile_kernel_name */
 VS_API int vs_tracker_get_profile(const struct vs_tracker* t, int32_t max_n, float* total_ms, int32_t* launches,

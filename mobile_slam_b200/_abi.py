@@ -58,7 +58,9 @@ EXPORTS = [
     "vs_tracker_last_device_ms", "vs_stage_clahe", "vs_stage_pyramid", "vs_stage_lk",
     "vs_stage_min_eig", "vs_stage_good_features", "vs_stage_undistort", "vs_stage_set_mask",
     "vs_stage_ransac", "vs_tracker_cuda_stream", "vs_tracker_set_profiling", "vs_tracker_get_profile",
-    "vs_profile_kernel_name", "vs_pack_image_features",
+    "vs_profile_kernel_name", "vs_pack_image_features", "vs_tracker_set_frontend_flags",
+    "vs_tracker_get_config", "vs_image_decode_gray", "vs_image_read_gray", "vs_ingest_create", "vs_ingest_submit_files",
+    "vs_ingest_submit_raw", "vs_ingest_wait", "vs_ingest_destroy",
 ]
 
 _lib = None
@@ -92,6 +94,16 @@ def load():
     lib.vs_tracker_submit_batch.argtypes = [vp, C.POINTER(vp), i32, C.POINTER(f64)]
     lib.vs_tracker_wait.argtypes = [vp, C.POINTER(VsTrackResult)]
     lib.vs_tracker_set_params.argtypes = [vp, i32, i32, f64, i32, i32, i32, f64, f64]
+    lib.vs_tracker_set_frontend_flags.argtypes = [vp, i32, i32, f64, vp, i32]
+    lib.vs_tracker_get_config.argtypes = [vp, C.POINTER(VsTrackerConfig)]
+    lib.vs_image_decode_gray.argtypes = [vp, i64, vp, i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]
+    lib.vs_image_read_gray.argtypes = [C.c_char_p, vp, i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]
+    lib.vs_ingest_create.argtypes = [vp, i32, C.POINTER(vp)]
+    lib.vs_ingest_submit_files.argtypes = [vp, C.POINTER(C.c_char_p), C.POINTER(f64)]
+    lib.vs_ingest_submit_raw.argtypes = [vp, C.POINTER(vp), i32, C.POINTER(f64)]
+    lib.vs_ingest_wait.argtypes = [vp, C.POINTER(VsTrackResult)]
+    lib.vs_ingest_destroy.argtypes = [vp]
+    lib.vs_ingest_destroy.restype = None
     lib.vs_tracker_set_reject_callback.argtypes = [vp, REJECT_FN, vp]
     lib.vs_tracker_reset.argtypes = [vp, i32]
     lib.vs_tracker_launch_count.argtypes = [vp]

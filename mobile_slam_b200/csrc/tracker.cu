@@ -119,6 +119,48 @@ static int upload_disc(vs_tracker* t) {
     return VS_OK;
 }
 
+// The mask setMask starts from (feature_tracker.cpp:40-60): all 255, or with `fisheye` the mask image if one is given,
+// else the auto-generated circle.  The reference builds its fisheye mask lazily on the first frame that has the flag
+// set and keeps it; here it is (re)built whenever the flag or the image changes (vs_tracker_set_frontend_flags).
+static int build_base_mask(vs_tracker* t, int fisheye, const uint8_t* mask_image, int mask_stride) {
+    GlueParams& g = t->g;
+    std::vector<uint8_t> m((size_t)g.mask_stride, 0);
+    const int W = t->W, H = t->H, mp = g.mask_pitch;
+    if (fisheye && mask_image) {
+        const int st = mask_stride > 0 ? mask_stride : W;
+        for (int y = 0; y < H; ++y) memcpy(&m[(size_t)y * mp], mask_image + (size_t)y * st, W);
+        t->base_mode = 2;
+    } else if (fisheye) {
+        const double cx = W / 2.0, cy = H / 2.0;
+        double rad = cx;
+        if (cy < rad) rad = cy;
+        if (W - cx < rad) rad = W - cx;
+        if (H - cy < rad) rad = H - cy;
+        rad *= 0.95;
+        const int icx = (int)cx, icy = (int)cy, r = (int)rad;
+        const std::vector<int> hw = circle_half_widths(r);
+        t->base_mode = 1;
+        t->fcx = icx;
+        t->fcy = icy;
+        t->fr = r;
+        VS_CUDA_TRY(cudaMemcpy(t->d_fish_hw, hw.data(), sizeof(int) * (r + 1), cudaMemcpyHostToDevice));
+        for (int dy = -r; dy <= r; ++dy) {
+            const int y = icy + dy, w = hw[dy < 0 ? -dy : dy];
+            if (y < 0 || y >= H || w < 0) continue;
+            int xa = icx - w, xb = icx + w;
+            if (xa < 0) xa = 0;
+            if (xb > W - 1) xb = W - 1;
+            for (int x = xa; x <= xb; ++x) m[(size_t)y * mp + x] = 255;
+        }
+    } else {
+        t->base_mode = 0;
+        for (int y = 0; y < H; ++y) memset(&m[(size_t)y * mp], 255, W);
+    }
+    VS_CUDA_TRY(cudaMemcpy(t->d_base_mask, m.data(), m.size(), cudaMemcpyHostToDevice));
+    t->cfg.fisheye = fisheye ? 1 : 0;
+    return VS_OK;
+}
+
 static void sync_glue_params(vs_tracker* t) {
     GlueParams& g = t->g;
     g.max_cnt = t->cfg.max_cnt;
@@ -424,40 +466,9 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     VS_TRY_CREATE(cudaMallocHost(&t->h_wnext, sizeof(float2) * B * C));
     VS_TRY_CREATE(cudaMallocHost(&t->h_rstatus, (size_t)(B * C)));
 
-    // base mask: feature_tracker.cpp:40-60
     {
-        std::vector<uint8_t> m((size_t)g.mask_stride, 0);
-        const int W = t->W, H = t->H, mp = g.mask_pitch;
-        if (cfg->fisheye && cfg->fisheye_mask_image) {
-            const int st = cfg->fisheye_mask_stride > 0 ? cfg->fisheye_mask_stride : W;
-            for (int y = 0; y < H; ++y) memcpy(&m[(size_t)y * mp], cfg->fisheye_mask_image + (size_t)y * st, W);
-            t->base_mode = 2;
-        } else if (cfg->fisheye) {
-            const double cx = W / 2.0, cy = H / 2.0;
-            double rad = cx;
-            if (cy < rad) rad = cy;
-            if (W - cx < rad) rad = W - cx;
-            if (H - cy < rad) rad = H - cy;
-            rad *= 0.95;
-            const int icx = (int)cx, icy = (int)cy, r = (int)rad;
-            const std::vector<int> hw = circle_half_widths(r);
-            t->base_mode = 1;
-            t->fcx = icx;
-            t->fcy = icy;
-            t->fr = r;
-            VS_TRY_CREATE(cudaMemcpy(t->d_fish_hw, hw.data(), sizeof(int) * (r + 1), cudaMemcpyHostToDevice));
-            for (int dy = -r; dy <= r; ++dy) {
-                const int y = icy + dy, w = hw[dy < 0 ? -dy : dy];
-                if (y < 0 || y >= H || w < 0) continue;
-                int xa = icx - w, xb = icx + w;
-                if (xa < 0) xa = 0;
-                if (xb > W - 1) xb = W - 1;
-                for (int x = xa; x <= xb; ++x) m[(size_t)y * mp + x] = 255;
-            }
-        } else {
-            for (int y = 0; y < H; ++y) memset(&m[(size_t)y * mp], 255, W);
-        }
-        VS_TRY_CREATE(cudaMemcpy(t->d_base_mask, m.data(), m.size(), cudaMemcpyHostToDevice));
+        const int rc = build_base_mask(t, cfg->fisheye, cfg->fisheye_mask_image, cfg->fisheye_mask_stride);
+        if (rc != VS_OK) { vs_tracker_destroy(t); return rc; }
     }
     {
         std::vector<int> ids((size_t)B, cfg->first_feature_id);
@@ -964,6 +975,43 @@ int vs_tracker_set_reject_callback(vs_tracker* t, vs_reject_fn fn, void* user) {
     if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
     t->reject_fn = fn;
     t->reject_user = user;
+    return VS_OK;
+}
+
+int vs_tracker_set_frontend_flags(vs_tracker* t, int32_t equalize, int32_t fisheye, double focal_length,
+                                  const uint8_t* fisheye_mask_image, int32_t fisheye_mask_stride) {
+    if (!t) { set_error("null tracker"); return VS_ERR_INVALID; }
+    if (t->submit_seq != t->wait_seq) { set_error("a submitted batch is still in flight: call vs_tracker_wait first"); return VS_ERR_STATE; }
+    for (vs_tracker* lane : t->lanes) {
+        const int rc = vs_tracker_set_frontend_flags(lane, equalize, fisheye, focal_length, fisheye_mask_image, fisheye_mask_stride);
+        if (rc != VS_OK) return rc;
+    }
+    if (equalize >= 0) t->cfg.equalize = equalize ? 1 : 0;          // read by the next frame's build_pyramid
+    if (focal_length > 0.0) t->cfg.focal_length = focal_length;       // read by the next frame's sync_glue_params
+    if (t->lanes.empty() && (fisheye >= 0 || fisheye_mask_image)) {
+        const int want = fisheye >= 0 ? (fisheye ? 1 : 0) : t->cfg.fisheye;
+        if (want != t->cfg.fisheye || fisheye_mask_image) {
+            VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+            VS_CUDA_TRY(cudaStreamSynchronize(t->stream));             // frames in flight still read the old mask
+            const int rc = build_base_mask(t, want, fisheye_mask_image, fisheye_mask_stride);
+            if (rc != VS_OK) return rc;
+        }
+    } else if (fisheye >= 0) {
+        t->cfg.fisheye = fisheye ? 1 : 0;
+    }
+    return VS_OK;
+}
+
+int vs_tracker_get_config(const vs_tracker* t, vs_tracker_config* out) {
+    if (!t || !out) { set_error("null argument"); return VS_ERR_INVALID; }
+    *out = t->cfg;
+    if (!t->lanes.empty()) {                       // the parent of a laned handle forwards set_params to its lanes
+        const vs_tracker_config& l = t->lanes[0]->cfg;
+        out->max_cnt = l.max_cnt; out->min_dist = l.min_dist; out->f_threshold = l.f_threshold;
+        out->lk_window_size = l.lk_window_size; out->lk_pyramid_levels = l.lk_pyramid_levels;
+        out->lk_iterations = l.lk_iterations; out->lk_eps = l.lk_eps; out->f_threshold_edge_factor = l.f_threshold_edge_factor;
+    }
+    out->fisheye_mask_image = nullptr;
     return VS_OK;
 }
 

@@ -223,6 +223,14 @@ class BatchTracker:
         _abi.check(self._lib.vs_tracker_set_params(self._h, max_cnt, min_dist, f_threshold, lk_window, lk_pyramid,
                                                    lk_iterations, lk_eps, f_edge_factor))
 
+    def set_frontend_flags(self, equalize=-1, fisheye=-1, focal_length=-1.0, fisheye_mask=None):
+        """g_config.feature_tracker.equalize / .fisheye (+ mask image) / camera.focal_length, which the reference re-reads
+        on every call (feature_tracker.cpp:39-46,102,214-222); tracking state is kept."""
+        m = None if fisheye_mask is None else np.ascontiguousarray(fisheye_mask, np.uint8)
+        _abi.check(self._lib.vs_tracker_set_frontend_flags(self._h, int(equalize), int(fisheye), float(focal_length),
+                                                           None if m is None else m.ctypes.data,
+                                                           0 if m is None else m.strides[0]))
+
     def set_reject_callback(self, fn):
         """fn(stream, un_cur (n,2) f32, un_next (n,2) f32, next_px (n,2) f32) -> status (n,) {0,1}."""
         if fn is None:
@@ -380,14 +388,36 @@ class FeatureTracker:
     def setCamera(self, cam: CameraParams):
         self._cam = cam
 
+    _RUNTIME = ("max_cnt", "min_dist", "f_threshold", "lk_window_size", "lk_pyramid_levels", "lk_iterations", "lk_eps",
+                "f_threshold_edge_factor")
+    _FLAGS = ("equalize", "fisheye", "focal_length")
+
     def _ensure(self):
         if self._bt is None:
             if self._cam is None:
                 raise RuntimeError("camera intrinsics not set (readIntrinsicParameter/setIntrinsicParameter)")
             self._bt = BatchTracker(self.config, self._cam, 1)
+            self._applied = {k: getattr(self.config, k) for k in self._RUNTIME + self._FLAGS}
+
+    def _apply_runtime_config(self):
+        """The reference reads ``g_config`` inside every call (feature_tracker.cpp:39-46,102,118-119,132-134,214-222):
+        changes to ``self.config`` between frames take effect on the next frame, tracking state kept."""
+        c, a = self.config, self._applied
+        if any(getattr(c, k) != a[k] for k in self._RUNTIME):
+            self._bt.set_params(c.max_cnt, c.min_dist, c.f_threshold, c.lk_window_size, c.lk_pyramid_levels,
+                                c.lk_iterations, c.lk_eps, c.f_threshold_edge_factor)
+        if any(getattr(c, k) != a[k] for k in self._FLAGS):
+            mask = c.fisheye_mask if (c.fisheye and not a["fisheye"]) else None
+            self._bt.set_frontend_flags(1 if c.equalize else 0, 1 if c.fisheye else 0, c.focal_length, mask)
+        self._applied = {k: getattr(c, k) for k in self._RUNTIME + self._FLAGS}
 
     def detectAndTrack(self, img, cur_time: float):
         self._ensure()
+        img = np.asarray(img)
+        if img.shape != (self.config.row, self.config.col):
+            # OpenCV throws in calcOpticalFlowPyrLK when the frame size changes; the handle's buffers are sized once
+            raise ValueError(f"image is {img.shape[1]}x{img.shape[0]}, camera.col x camera.row is {self.config.col}x{self.config.row}")
+        self._apply_runtime_config()
         self.cur_time = float(cur_time)
         r = self._bt.track([img], [cur_time])[0]
         self.cur_pts = r.cur_pts

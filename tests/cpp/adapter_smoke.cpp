@@ -24,15 +24,22 @@ int main(int argc, char** argv) {
             tc.width = W; tc.height = H; tc.max_cnt = 60; tc.min_dist = 20; tc.ransac_mode = VS_RANSAC_OFF;
             tc.camera.width = W; tc.camera.height = H; tc.camera.fx = tc.camera.fy = 300.0; tc.camera.cx = W / 2.0; tc.camera.cy = H / 2.0;
             vs::ShardedTracker st(tc, S, G, 2);
-            std::vector<const uint8_t*> fr(S);
-            std::vector<double> ts(S);
+            // persistent per-GPU workers, two batches in flight: submit frame k+1 before waiting for frame k
+            std::vector<std::vector<const uint8_t*>> fr(N, std::vector<const uint8_t*>(S));
+            std::vector<std::vector<double>> ts(N, std::vector<double>(S));
+            for (int k = 0; k < N; ++k)
+                for (int s = 0; s < S; ++s) { fr[k][s] = buf.data() + (size_t)k * W * H; ts[k][s] = 0.05 * k; }
+            st.submit(fr[0].data(), W, ts[0].data());
             for (int k = 0; k < N; ++k) {
-                for (int s = 0; s < S; ++s) { fr[s] = buf.data() + (size_t)k * W * H; ts[s] = 0.05 * k; }
-                const auto& r = st.track(fr.data(), W, ts.data());
+                if (k + 1 < N) st.submit(fr[k + 1].data(), W, ts[k + 1].data());
+                const auto& r = st.wait();
                 for (int s = 1; s < S; ++s)
                     if (r[s].n != r[0].n || std::memcmp(r[s].cur_pts, r[0].cur_pts, sizeof(float) * 2 * r[0].n)) { std::printf("stream %d differs\n", s); return 1; }
                 std::printf("%d %d\n", k, r[0].n);
             }
+            // and the synchronous form on top of the same workers
+            const auto& r2 = st.track(fr[N - 1].data(), W, ts[N - 1].data());
+            if (r2[0].n <= 0) { std::printf("track() returned nothing\n"); return 1; }
             std::printf("sharded ok %d gpus %d streams\n", st.n_gpus(), st.n_streams());
             return 0;
         }

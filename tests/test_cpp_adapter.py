@@ -84,3 +84,62 @@ def test_adapter_matches_python_mirror(tmp_path, built_lib):
     # stream-sharded host layer on one GPU: 5 identical streams -> identical tracks
     out = subprocess.run([str(exe), str(p), "320", "240", "6", "-", "1", "5"], capture_output=True, text=True)
     assert out.returncode == 0 and "sharded ok 1 gpus 5 streams" in out.stdout, out.stdout + out.stderr
+
+
+def _build_opencv_probe(tmp_path, use_reference_headers):
+    """the configuration INTEGRATION.md §2 prescribes: -DVS_WITH_OPENCV -DVS_WITH_REFERENCE_CONFIG (OpenCV = the stand-in
+    of oracle/ref_shim; utility/config.h = the reference's own header where /root/reference exists, else tests/cpp/stubs)"""
+    exe = tmp_path / ("probe_ref" if use_reference_headers else "probe_stub")
+    inc = ["-I", "/root/reference/include"] if use_reference_headers else ["-I", os.path.join(ROOT, "tests", "cpp", "stubs")]
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-DVS_WITH_OPENCV", "-DVS_WITH_REFERENCE_CONFIG",
+                           "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "oracle", "ref_shim"), *inc,
+                           os.path.join(ROOT, "tests", "cpp", "adapter_opencv_probe.cpp"), "-o", str(exe),
+                           "-L", PKG, "-lvs_tracker", f"-Wl,-rpath,{PKG}", "-lpthread"])
+    return exe
+
+
+def test_adapter_compiles_with_opencv_and_reference_config(tmp_path, built_lib):
+    import torch
+    exes = [_build_opencv_probe(tmp_path, False)]
+    if os.path.exists("/root/reference/include/utility/config.h"):
+        exes.append(_build_opencv_probe(tmp_path, True))        # against the reference's real utility/config.h
+    p, _ = _frames(tmp_path, 2)
+    for exe in exes:
+        r = subprocess.run([str(exe), str(p), "320", "240", "2"], capture_output=True, text=True)
+        if torch.cuda.is_available():
+            assert r.returncode == 0, r.stderr
+        else:
+            assert r.returncode == 3 and "no CPU fallback" in r.stderr, (r.returncode, r.stderr)
+
+
+@pytest.mark.gpu
+def test_adapter_opencv_mode_follows_g_config(tmp_path, built_lib):
+    """cv::Mat frames, utility::g_config re-read on every call (max_cnt, LK criteria, equalize mutated between frames)
+    == the Python mirror driven with the same changes; a frame of another size is refused."""
+    from mobile_slam_b200 import FeatureTracker, TrackerConfig, VS_RANSAC_OFF, VS_CAM_PINHOLE
+    exe = _build_opencv_probe(tmp_path, False)
+    p, fr = _frames(tmp_path, 7)
+    out = subprocess.run([str(exe), str(p), "320", "240", "7"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    lines = out.stdout.strip().splitlines()
+    assert lines[-1] == "size change refused"
+    ft = FeatureTracker(TrackerConfig(col=320, row=240, max_cnt=60, min_dist=20, ransac_mode=VS_RANSAC_OFF, capacity=1024))
+    ft.setIntrinsicParameter(VS_CAM_PINHOLE, 320, 240, 300.0, 300.0, 160.0, 120.0, -0.1, 0.01, 1e-4, -1e-4)
+    for k in range(7):
+        if k == 2:
+            ft.config.max_cnt = 80                     # the mirror re-reads its config on every call, like g_config
+        if k == 3:
+            ft.config.lk_window_size, ft.config.lk_iterations, ft.config.lk_eps = 15, 20, 0.03
+        if k == 4:
+            ft.config.equalize = 0
+        ft.detectAndTrack(fr[k], 0.05 * k)
+        i = 0
+        while ft.updateID(i):
+            i += 1
+        tok = lines[k].split()
+        assert int(tok[0]) == k and int(tok[1]) == len(ft.ids) and int(tok[2]) == len(ft.image_data()), (k, tok[:3], len(ft.ids))
+        for j in range(min(4, len(ft.ids))):
+            t = tok[3 + 4 * j: 7 + 4 * j]
+            assert int(t[0]) == ft.ids[j] and int(t[3]) == ft.track_cnt[j]
+            assert abs(float(t[1]) - ft.cur_pts[j][0]) < 1e-5 and abs(float(t[2]) - ft.cur_pts[j][1]) < 1e-5
+    assert len(ft.ids) > 60          # max_cnt 80 took effect

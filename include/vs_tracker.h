@@ -187,6 +187,12 @@ VS_API int vs_stage_set_mask(struct vs_tracker* t, const float* pts_xy, const in
                       int32_t* keep_idx, int32_t* n_keep);
 /* F-matrix RANSAC on virtual-pinhole points (device implementation) */
 VS_API int vs_stage_ransac(struct vs_tracker* t, const float* a_xy, const float* b_xy, int32_t n, uint8_t* status);
+/* Flags for a GIVEN fundamental matrix f9 (row-major, x2^T F x1 = 0): base_status == NULL -> inlier test (both epipolar
+ * distances <= f_threshold) + the reference's edge recovery (feature_tracker.cpp:236-285, edge_factor > 0); base_status
+ * != NULL -> those flags (e.g. cv::findFundamentalMat's own mask) + only the edge-recovery rule.  Teacher-forced parity. */
+VS_API int vs_stage_ransac_mark(struct vs_tracker* t, const double* f9, const float* a_xy, const float* b_xy,
+                                const float* next_px_xy, int32_t n, double edge_factor, const uint8_t* base_status,
+                                uint8_t* status);
 /* ---- measurement hooks (bench.py) ---- */
 /* The handle's CUDA stream (a cudaStream_t): lets a caller record its own events on the stream the
  * kernels are launched on, or order its own work after a track call. */

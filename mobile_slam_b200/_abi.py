@@ -60,7 +60,7 @@ EXPORTS = [
     "vs_stage_ransac", "vs_tracker_cuda_stream", "vs_tracker_set_profiling", "vs_tracker_get_profile",
     "vs_profile_kernel_name", "vs_pack_image_features", "vs_tracker_set_frontend_flags",
     "vs_tracker_get_config", "vs_image_decode_gray", "vs_image_read_gray", "vs_ingest_create", "vs_ingest_submit_files",
-    "vs_ingest_submit_raw", "vs_ingest_wait", "vs_ingest_destroy",
+    "vs_ingest_submit_raw", "vs_ingest_wait", "vs_ingest_destroy", "vs_stage_ransac_mark",
 ]
 
 _lib = None
@@ -118,6 +118,7 @@ def load():
     lib.vs_stage_undistort.argtypes = [vp, vp, i32, vp]
     lib.vs_stage_set_mask.argtypes = [vp, vp, vp, i32, vp, C.POINTER(i32)]
     lib.vs_stage_ransac.argtypes = [vp, vp, vp, i32, vp]
+    lib.vs_stage_ransac_mark.argtypes = [vp, vp, vp, vp, vp, i32, f64, vp, vp]
     lib.vs_tracker_cuda_stream.argtypes = [vp]
     lib.vs_tracker_cuda_stream.restype = vp
     lib.vs_tracker_set_profiling.argtypes = [vp, i32]

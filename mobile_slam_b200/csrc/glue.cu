@@ -456,6 +456,8 @@ __device__ __forceinline__ void set_mask_body(const GlueParams& g, const int s, 
         g.want[s] = want;
         g.cand_count[s] = 0;
         g.max_enc[s] = 0;
+        g.raw_count[s] = 0;
+        g.l_enc[s] = 0;
         int* h = g.r_hdr + (int64_t)s * kHdrInts;
         h[H_RANSAC_OUT] = n2;
         h[H_MASK_KEPT] = kn;

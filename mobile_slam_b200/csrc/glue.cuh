@@ -70,6 +70,9 @@ struct GlueParams {
     int* cand_count;           // [B]
     int cand_cap;
     unsigned int* max_enc;     // [B]
+    unsigned long long* cand_raw;   // [B][cand_cap] two-tier Shi-Tomasi: records awaiting exact evaluation
+    int* raw_count;            // [B]
+    unsigned int* l_enc;       // [B] lower bound of the masked max (fp32 scan)
 
     // results (device mirror of the pinned host block)
     int* r_hdr;                // [B][kHdrInts]

@@ -22,6 +22,9 @@ void launch_copy_image(const uint8_t* src, int src_pitch, int64_t src_stride, ui
 void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from, int n_streams, cudaStream_t st,
                      int64_t* launches);
 
+// REFLECT_101 border (kPyrPadX / kPyrPadY) of levels 0 .. n_levels-1, one launch
+void launch_pyr_pad(uint8_t* pyr_base, const PyrDesc& pd, int n_levels, int n_streams, cudaStream_t st, int64_t* launches);
+
 // ---- lk.cu (K9) ----
 struct LkParams {
     const uint8_t* prev_pyr;
@@ -65,6 +68,11 @@ struct StParams {
     unsigned long long* cand; // [n_streams][cand_cap] (eig bits << 32 | y*W + x)
     int* cand_count;          // [n_streams]
     int cand_cap;
+    // two-tier frame path (st_scan_kernel -> st_refine_kernel): records of the pixels that may be candidates / the
+    // masked maximum, and the running lower bound of that maximum; null = one-pass exact kernel
+    unsigned long long* raw;  // [n_streams][cand_cap] (neighbours' max upper bound bits << 32 | flags | y*W + x)
+    int* raw_count;           // [n_streams]
+    unsigned int* l_enc;      // [n_streams] order-preserving encoding of a lower bound of the masked max
     float* eig_out;           // optional dense eig map [n_streams][H][W] (stage tests), else null
     uint8_t* mask_out;        // optional mask image [n_streams][H][mask_out_pitch] (stage tests), else null
     int mask_out_pitch;

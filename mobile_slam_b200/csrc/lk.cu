@@ -216,13 +216,13 @@ __global__ void __launch_bounds__(32 * kLkWarpsPerCta) lk_kernel(LkParams p) {
 
 // =================================================================================================
 // Fast path (win = 21): every lane owns two horizontal runs of 7 window pixels (21 rows x 3 runs = 63
-// runs for 32 lanes x 2).  Tiles are staged as aligned 32-bit words; a run reads 3 words per tile
+// runs for 32 lanes x 2).  Tiles are staged as 16-byte chunks (cp.async); a run reads 3 words per tile
 // row and re-aligns them with funnel shifts, the bilinear blend is two DP2A per pixel (16-bit
 // weights x u8 pixels), the Scharr derivatives five DP4A per sample, and the mismatch vector is
 // accumulated as sum(J*Ix) - sum(I*Ix) with the second term fixed per level.  All integer and
 // exact, so results are bit-identical to the generic kernel above.
 // =================================================================================================
-constexpr int kFastPitch = 36;                 // tile pitch in bytes (9 words)
+constexpr int kFastPitch = 48;                 // tile pitch in bytes: three 16-byte chunks per row
 constexpr int kFastRows = 32;                  // search tile rows = win + 1 + 2 * margin
 constexpr int kFastWarpSmem = kFastPitch * kFastRows;
 
@@ -242,56 +242,26 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
     return d;
 }
 
-// stage NROWS x NWORDS aligned words of a level into the warp's tile; x0 is a multiple of 4.
-// Fully unrolled: when the tile lies inside the level (the common case, warp-uniform test) a lane issues
-// all of its loads back to back before the first shared-memory store, so 6..9 requests are in flight.
-template <int NROWS, int NWORDS>
-__device__ __forceinline__ void stage_words(uint32_t* tile, const uint8_t* __restrict__ img, int w, int h, int pitch,
-                                            int x0, int y0, int lane) {
-    constexpr int TOTAL = NROWS * NWORDS, U = (TOTAL + 31) / 32;
-    constexpr int DR = 32 / NWORDS, DQ = 32 % NWORDS;
-    int r = lane / NWORDS, q = lane - r * NWORDS;
-    const bool interior = x0 >= 0 && y0 >= 0 && x0 + 4 * NWORDS <= w && y0 + NROWS <= h;
-    if (interior) {
-        const uint8_t* base = img + (int64_t)y0 * pitch + x0;
-        uint32_t v[U];
-        int off[U];
+// Stage NROWS rows of 48 bytes of a level into the warp's tile; x0 is a multiple of 16.  Every level carries a REFLECT_101
+// border (kPyrPadX x kPyrPadY, written by pyr_pad_*_kernel), which covers every tile this kernel can ask for (origins
+// down to -48 columns / -26 rows, ends up to w + 42 / h + 26), so each 16-byte chunk goes global -> shared with ONE
+// asynchronous copy (cp.async.cg, 128 bits, no register staging, no border handling): 3 instructions per lane for a whole
+// search tile.  Pitches and level offsets are multiples of 16, so every chunk is 16-byte aligned on both sides.
+template <int NROWS>
+__device__ __forceinline__ void stage_rows16(uint32_t* tile, const uint8_t* __restrict__ img, int pitch, int x0, int y0, int lane) {
+    constexpr int CH = kFastPitch / 16, TOTAL = NROWS * CH, U = (TOTAL + 31) / 32;
+    static_assert(kPyrPadX >= kFastPitch && kPyrPadY >= 21 + 1 + kLkMargin, "level border too small for the tiles");
+    const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(tile);
+    const uint8_t* src = img + (int64_t)y0 * pitch + x0;
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const bool ok = (u < U - 1) || (lane + 32 * u < TOTAL);
-            off[u] = r * (kFastPitch / 4) + q;
-            v[u] = ok ? __ldg(reinterpret_cast<const uint32_t*>(base + (int64_t)r * pitch) + q) : 0u;
-            r += DR;
-            q += DQ;
-            if (q >= NWORDS) {
-                q -= NWORDS;
-                ++r;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-            if ((u < U - 1) || (lane + 32 * u < TOTAL)) tile[off[u]] = v[u];
-    } else {
-#pragma unroll 1
-        for (int idx = lane; idx < TOTAL; idx += 32) {
-            const int gx = x0 + 4 * q, gy = y0 + r;
-            uint32_t v;
-            if (gy >= 0 && gy < h && gx >= 0 && gx + 3 < w) {
-                v = __ldg(reinterpret_cast<const uint32_t*>(img + (int64_t)gy * pitch + gx));
-            } else {
-                const uint8_t* row = img + (int64_t)reflect101(gy, h) * pitch;
-                v = (uint32_t)__ldg(row + reflect101(gx, w)) | ((uint32_t)__ldg(row + reflect101(gx + 1, w)) << 8) |
-                    ((uint32_t)__ldg(row + reflect101(gx + 2, w)) << 16) | ((uint32_t)__ldg(row + reflect101(gx + 3, w)) << 24);
-            }
-            tile[r * (kFastPitch / 4) + q] = v;
-            r += DR;
-            q += DQ;
-            if (q >= NWORDS) {
-                q -= NWORDS;
-                ++r;
-            }
-        }
+    for (int u = 0; u < U; ++u) {
+        const int idx = lane + 32 * u;
+        if (U * 32 != TOTAL && idx >= TOTAL) break;
+        const int r = idx / CH, c = idx - r * CH;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_s + (uint32_t)(r * kFastPitch + 16 * c)),
+                     "l"(src + (int64_t)r * pitch + 16 * c) : "memory");
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 // 12 bytes of a tile row starting at byte `sb`, re-aligned so that a0 holds bytes sb..sb+3, a1 sb+4..sb+7, a2 sb+8..sb+11
@@ -349,10 +319,10 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
         lk_weights(__fsub_rn(ppx, (float)ipx), __fsub_rn(ppy, (float)ipy), w00, w01, w10, w11);
         int wt = (w00 & 0xffff) | (w01 << 16), wb = (w10 & 0xffff) | (w11 << 16);
 
-        // ---- template: tile origin (x aligned down to 4, ipy - 1), 24 rows x 8 words ----
-        const int tx0 = (ipx - 1) & ~3, ax = (ipx - 1) - tx0;
+        // ---- template: tile origin (x aligned down to 16, ipy - 1), 24 rows x 48 bytes ----
+        const int tx0 = (ipx - 1) & ~15, ax = (ipx - 1) - tx0;
         __syncwarp();
-        stage_words<WIN + 3, 8>(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, lane);
+        stage_rows16<WIN + 3>(tile, prev_base + L.offset, L.pitch, tx0, ipy - 1, lane);
         __syncwarp();
         const bool border = ipx < 0 || ipy < 0 || ipx + WIN + 1 > L.w || ipy + WIN + 1 > L.h;
         int s11 = 0, s12 = 0, s22 = 0;
@@ -432,7 +402,7 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
         float qx = __fsub_rn(next.x, hw), qy = __fsub_rn(next.y, hw);
         float pdx = 0.f, pdy = 0.f;
         const uint8_t* J = next_base + L.offset;
-        int tox = 0, toy = 0;          // image coordinates of tile byte (0, 0); tox is a multiple of 4
+        int tox = 0, toy = 0;          // image coordinates of tile byte (0, 0); tox is a multiple of 16
         bool staged = false;
         for (int j = 0; j < p.max_count; ++j) {
             const int iqx = (int)floorf(qx), iqy = (int)floorf(qy);
@@ -442,10 +412,10 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
             }
             // the tile must hold columns iqx .. iqx+21 (+ alignment slack) and rows iqy .. iqy+21
             if (!staged || iqx < tox || iqx + WIN + 1 + 3 > tox + kFastPitch || iqy < toy || iqy + WIN + 1 > toy + kFastRows) {
-                tox = (iqx - kLkMargin) & ~3;
+                tox = (iqx - kLkMargin) & ~15;
                 toy = iqy - kLkMargin;
                 __syncwarp();
-                stage_words<kFastRows, kFastPitch / 4>(tile, J, L.w, L.h, L.pitch, tox, toy, lane);
+                stage_rows16<kFastRows>(tile, J, L.pitch, tox, toy, lane);
                 __syncwarp();
                 staged = true;
             }

@@ -134,6 +134,59 @@ __global__ void __launch_bounds__(32 * kPdWarps) pyr_down_kernel(const uint8_t* 
     }
 }
 
+// ---- REFLECT_101 border of every built level (cv::buildOpticalFlowPyramid stores its levels padded the same way) -----
+// One launch for all levels: a warp takes kPadRowsPerWarp rows of the PADDED level (rows -kPyrPadY .. h + kPyrPadY - 1).
+// For every row it writes the column border — the 48 bytes left of the row and everything from the last aligned word of
+// the row to the end of the pitch, one aligned word per lane assembled from reflected bytes of source row
+// reflect101(y) — and, for the rows above / below the level, a 16-byte copy of that source row's interior.  Only border
+// bytes are written and only interior bytes are read, so no ordering between warps is needed.
+constexpr int kPadWarps = 8, kPadRowsPerWarp = 4;
+
+__global__ void __launch_bounds__(32 * kPadWarps) pyr_pad_kernel(uint8_t* __restrict__ pyr, PyrDesc pd, int n_levels) {
+    pdl_entry();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* sbase = pyr + (int64_t)blockIdx.y * pd.stream_bytes;
+    constexpr int NL = kPyrPadX / 4;
+#pragma unroll 1
+    for (int i = 0; i < kPadRowsPerWarp; ++i) {
+        int idx = (blockIdx.x * kPadWarps + warp) * kPadRowsPerWarp + i, l = 0;
+        for (; l < n_levels; ++l) {
+            const int n = pd.lv[l].h + 2 * kPyrPadY;
+            if (idx < n) break;
+            idx -= n;
+        }
+        if (l == n_levels) return;
+        const LevelDesc L = pd.lv[l];
+        const int y = idx - kPyrPadY;
+        const uint8_t* srow = sbase + L.offset + (int64_t)reflect101(y, L.h) * L.pitch;
+        uint8_t* drow = sbase + L.offset + (int64_t)y * L.pitch;
+        const int xr0 = L.w & ~3, nright = (L.pitch - kPyrPadX - xr0) >> 2;
+        int x0 = 0x7fffffff;
+        if (lane < NL) x0 = -kPyrPadX + 4 * lane;
+        else if (lane - NL < nright) x0 = xr0 + 4 * (lane - NL);
+        if (x0 != 0x7fffffff) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(srow + reflect101(x0 + b, L.w)) << (8 * b);   // in-range bytes map to themselves
+            *reinterpret_cast<uint32_t*>(drow + x0) = v;
+        }
+        if (y < 0 || y >= L.h) {
+            const int n16 = xr0 >> 4;
+            for (int c = lane; c < n16; c += 32) reinterpret_cast<uint4*>(drow)[c] = __ldg(reinterpret_cast<const uint4*>(srow) + c);
+            for (int c = (n16 << 2) + lane; c < (xr0 >> 2); c += 32)
+                reinterpret_cast<uint32_t*>(drow)[c] = __ldg(reinterpret_cast<const uint32_t*>(srow) + c);
+        }
+    }
+}
+
+void launch_pyr_pad(uint8_t* pyr_base, const PyrDesc& pd, int n_levels, int n_streams, cudaStream_t st, int64_t* launches) {
+    int rows = 0;
+    for (int l = 0; l < n_levels; ++l) rows += pd.lv[l].h + 2 * kPyrPadY;
+    const int per_cta = kPadWarps * kPadRowsPerWarp;
+    launch_pdl(pyr_pad_kernel, dim3((rows + per_cta - 1) / per_cta, n_streams), dim3(32 * kPadWarps), 0, st, pyr_base, pd, n_levels);
+    if (launches) *launches += 1;
+}
+
 void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from, int n_streams, cudaStream_t st,
                      int64_t* launches) {
     const LevelDesc& a = pd.lv[level_from];

@@ -256,6 +256,34 @@ __device__ __forceinline__ void block_sums(double* v, double (*s_red)[4], int ti
     }
 }
 
+// Final flags for a given model F (row-major, x2^T F x1 = 0): inlier iff the larger of the two point-to-epipolar-line
+// distances is within f_threshold (what cv::findFundamentalMat's RANSAC reports), then the reference's distance-aware edge
+// recovery (feature_tracker.cpp:236-285) for the rejected points.  keep_base = true takes the inlier flags already in
+// w_rstatus (a teacher's, e.g. cv2's own mask) and applies only the recovery rule.
+__device__ __forceinline__ void ransac_mark(const GlueParams& g, int64_t o, int n, const double* F, const float2* pa,
+                                            const float2* pb, bool keep_base, int tid, int nthreads) {
+    const double t2 = g.f_threshold * g.f_threshold;
+    const double ef = g.f_edge_factor;
+    const double dcx = (double)g.W / 2.0, dcy = (double)g.H / 2.0;
+    const double r_max = sqrt(dcx * dcx + dcy * dcy), r_max_inv = r_max > 1e-6 ? 1.0 / r_max : 0.0;
+    for (int i = tid; i < n; i += nthreads) {
+        const double x1 = pa[i].x, y1 = pa[i].y, x2 = pb[i].x, y2 = pb[i].y;
+        const double a = F[0] * x1 + F[1] * y1 + F[2], b = F[3] * x1 + F[4] * y1 + F[5], c = F[6] * x1 + F[7] * y1 + F[8];
+        const double d = x2 * a + y2 * b + c;
+        const double a2 = F[0] * x2 + F[3] * y2 + F[6], b2 = F[1] * x2 + F[4] * y2 + F[7];
+        const double smin = fmin(a * a + b * b, a2 * a2 + b2 * b2);
+        bool in = keep_base ? (g.w_rstatus[o + i] != 0) : (d * d <= t2 * smin);
+        if (!in && ef > 0.0) {                   // edge recovery, feature_tracker.cpp:236-285
+            const float2 px = g.w_next[o + i];
+            const double dx = (double)px.x - dcx, dy = (double)px.y - dcy;
+            const double rr = sqrt(dx * dx + dy * dy) * r_max_inv;
+            const double nab = sqrt(a * a + b * b);
+            if (rr >= 0.3 && nab >= 1e-12) in = fabs(d) / nab < g.f_threshold * (1.0 + ef * rr * rr);
+        }
+        g.w_rstatus[o + i] = in ? 1 : 0;
+    }
+}
+
 // One stream's RANSAC; every thread of a 256-thread CTA calls it (dsm = 16 * cap bytes of dynamic shared memory).
 __device__ __forceinline__ void ransac_body(const GlueParams& g, const unsigned int seed, const int s, const int tid, uint8_t* dsm) {
     float2* pa = reinterpret_cast<float2*>(dsm);          // [cap] image-1 (cur) points, centred
@@ -360,26 +388,7 @@ __device__ __forceinline__ void ransac_body(const GlueParams& g, const unsigned 
     for (int w = 1; w < kRansacWarps; ++w) wb = s_key[par ^ 1][w] == best ? w : wb;
     double F[9];
     for (int c = 0; c < 9; ++c) F[c] = s_bestF[wb][c];
-    const double t2 = g.f_threshold * g.f_threshold;
-    const double ef = g.f_edge_factor;
-    const double dcx = (double)g.W / 2.0, dcy = (double)g.H / 2.0;
-    const double r_max = sqrt(dcx * dcx + dcy * dcy), r_max_inv = r_max > 1e-6 ? 1.0 / r_max : 0.0;
-    for (int i = tid; i < n; i += kRansacThreads) {
-        const double x1 = pa[i].x, y1 = pa[i].y, x2 = pb[i].x, y2 = pb[i].y;
-        const double a = F[0] * x1 + F[1] * y1 + F[2], b = F[3] * x1 + F[4] * y1 + F[5], c = F[6] * x1 + F[7] * y1 + F[8];
-        const double d = x2 * a + y2 * b + c;
-        const double a2 = F[0] * x2 + F[3] * y2 + F[6], b2 = F[1] * x2 + F[4] * y2 + F[7];
-        const double smin = fmin(a * a + b * b, a2 * a2 + b2 * b2);
-        bool in = d * d <= t2 * smin;
-        if (!in && ef > 0.0) {                   // edge recovery, feature_tracker.cpp:236-285
-            const float2 px = g.w_next[o + i];
-            const double dx = (double)px.x - dcx, dy = (double)px.y - dcy;
-            const double rr = sqrt(dx * dx + dy * dy) * r_max_inv;
-            const double nab = sqrt(a * a + b * b);
-            if (rr >= 0.3 && nab >= 1e-12) in = fabs(d) / nab < g.f_threshold * (1.0 + ef * rr * rr);
-        }
-        g.w_rstatus[o + i] = in ? 1 : 0;
-    }
+    ransac_mark(g, o, n, F, pa, pb, false, tid, kRansacThreads);
 }
 
 

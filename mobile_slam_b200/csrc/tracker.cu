@@ -55,9 +55,9 @@ static void plan_pyramid(vs_tracker* t) {
     for (int l = 0; l < kMaxLevels; ++l) {
         pd.lv[l].w = w;
         pd.lv[l].h = h;
-        pd.lv[l].pitch = round_up(w, 16);
-        pd.lv[l].offset = off;
-        off += (int64_t)round_up(pd.lv[l].pitch * h, 256);
+        pd.lv[l].pitch = round_up(w + 2 * kPyrPadX, 16);
+        pd.lv[l].offset = off + (int64_t)kPyrPadY * pd.lv[l].pitch + kPyrPadX;      // pixel (0, 0) inside the padded block
+        off += (int64_t)round_up(pd.lv[l].pitch * (h + 2 * kPyrPadY), 256);
         w = (w + 1) / 2;
         h = (h + 1) / 2;
         if (w < 1) w = 1;
@@ -443,12 +443,19 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     VS_TRY_CREATE(A.alloc(&t->d_base_mask, (size_t)g.mask_stride));
     g.base_mask = t->d_base_mask;
     g.disc_hw = t->d_disc_hw;
-    int cc = 1;
-    while (cc < (t->W * t->H + 3) / 4) cc <<= 1;       // strict 3x3 local maxima cannot exceed P/4
+    // 3x3 NMS is non-strict (v >= neighbours, like OpenCV's eig == dilate(eig)), so plateaus of equal response can make
+    // every pixel of a region a candidate: size the list for the whole image, then nothing is ever dropped
+    const int cc = round_up(t->W * t->H, 64);
     g.cand_cap = cc;
     VS_TRY_CREATE(A.alloc(&g.cand, (size_t)(B * cc), false));
     VS_TRY_CREATE(A.alloc(&g.cand_count, B));
     VS_TRY_CREATE(A.alloc(&g.max_enc, B));
+    {   // the record list of the two-tier Shi-Tomasi variant, only when that variant is selected (A/B runs)
+        const char* e = getenv("VS_ST_TWO_TIER");
+        if (e && atoi(e) != 0) VS_TRY_CREATE(A.alloc(&g.cand_raw, (size_t)(B * cc), false));
+    }
+    VS_TRY_CREATE(A.alloc(&g.raw_count, B));
+    VS_TRY_CREATE(A.alloc(&g.l_enc, B));
     // results block: hdr | ids | cnt | pts | un | vel
     t->h_block_bytes = (size_t)(B * kHdrInts * 4 + B * C * (4 + 4 + 8 + 8 + 8));
     VS_TRY_CREATE(A.alloc(&t->d_rblock, t->h_block_bytes));
@@ -562,6 +569,7 @@ static int build_pyramid(vs_tracker* t, int buf, const uint8_t* d_img, int pitch
     }
     const int nl = levels_to_build(t);
     for (int l = 0; l + 1 < nl; ++l) launch_pyr_down(t->d_pyr[buf], t->pd, l, t->B, t->stream, &t->launches);
+    launch_pyr_pad(t->d_pyr[buf], t->pd, nl, t->B, t->stream, &t->launches);
     prof_tick(t, PK_PYR_DOWN);
     t->built[buf] = nl;
     return VS_OK;
@@ -619,6 +627,9 @@ static StParams make_st_params(vs_tracker* t, int buf, const GlueParams& g) {
     e.cand = g.cand;
     e.cand_count = g.cand_count;
     e.cand_cap = g.cand_cap;
+    e.raw = g.cand_raw;
+    e.raw_count = g.raw_count;
+    e.l_enc = g.l_enc;
     e.eig_out = nullptr;
     e.mask_out = nullptr;
     e.quality = 0.01;
@@ -1169,6 +1180,7 @@ int vs_stage_lk(vs_tracker* t, const uint8_t* prev_level0, const uint8_t* next_l
         rc = upload_level0(t, b, b == 0 ? prev_level0 : next_level0);
         if (rc != VS_OK) return rc;
         for (int l = 0; l + 1 < nl; ++l) launch_pyr_down(t->d_pyr[b], t->pd, l, 1, t->stream, &t->launches);
+        launch_pyr_pad(t->d_pyr[b], t->pd, nl, 1, t->stream, &t->launches);
         t->built[b] = nl;
     }
     VS_CUDA_TRY(cudaMemcpyAsync(t->g.pts, pts_xy, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, t->stream));
@@ -1189,6 +1201,8 @@ static int stage_prepare_mask(vs_tracker* t, const float* kept_xy, int n_kept, i
     VS_CUDA_TRY(cudaMemcpyAsync(g1.want, &want, sizeof(int), cudaMemcpyHostToDevice, t->stream));
     VS_CUDA_TRY(cudaMemsetAsync(g1.cand_count, 0, sizeof(int), t->stream));
     VS_CUDA_TRY(cudaMemsetAsync(g1.max_enc, 0, sizeof(int), t->stream));
+    VS_CUDA_TRY(cudaMemsetAsync(g1.raw_count, 0, sizeof(int), t->stream));
+    VS_CUDA_TRY(cudaMemsetAsync(g1.l_enc, 0, sizeof(int), t->stream));
     return VS_OK;
 }
 

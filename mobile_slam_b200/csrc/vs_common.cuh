@@ -17,6 +17,13 @@ struct LevelDesc {
     int64_t offset;        // byte offset of the level inside one stream's pyramid block
 };
 
+// Every level is stored with a REFLECT_101 border of kPyrPadX columns / kPyrPadY rows (what cv::buildOpticalFlowPyramid
+// stores too): LevelDesc::offset addresses pixel (0, 0), rows -kPyrPadY .. h + kPyrPadY - 1 and columns -kPyrPadX ..
+// pitch - kPyrPadX - 1 exist.  The LK kernel's 48 x 32-byte search tiles (16-byte chunks, origin up to 48 columns / 26 rows
+// outside the level) then never need border handling.
+constexpr int kPyrPadX = 48;       // multiple of 16
+constexpr int kPyrPadY = 32;
+
 struct PyrDesc {
     int n_levels;          // levels actually built (<= maxLevel+1)
     LevelDesc lv[kMaxLevels];

@@ -335,6 +335,19 @@ class BatchTracker:
         return st
 
     # ---- measurement hooks -------------------------------------------------------------------
+    def stage_ransac_mark(self, F, a, b, next_px, edge_factor=0.0, base_status=None):
+        """flags the device assigns for a GIVEN fundamental matrix (teacher forcing); base_status = a teacher's inlier
+        mask -> only the edge-recovery rule of feature_tracker.cpp:236-285 is applied on top of it"""
+        F = np.ascontiguousarray(F, np.float64).reshape(9)
+        a = np.ascontiguousarray(a, np.float32).reshape(-1, 2)
+        b = np.ascontiguousarray(b, np.float32).reshape(-1, 2)
+        px = np.ascontiguousarray(next_px, np.float32).reshape(-1, 2)
+        st = np.zeros(len(a), np.uint8)
+        base = None if base_status is None else np.ascontiguousarray(base_status, np.uint8)
+        _abi.check(self._lib.vs_stage_ransac_mark(self._h, F.ctypes.data, a.ctypes.data, b.ctypes.data, px.ctypes.data, len(a),
+                                                  float(edge_factor), None if base is None else base.ctypes.data, st.ctypes.data))
+        return st
+
     @property
     def cuda_stream(self) -> int:
         """cudaStream_t of the handle (wrap with torch.cuda.ExternalStream to record events on it)."""

@@ -218,29 +218,7 @@ class RefFeatureTracker:
         if status is None:
             status = np.zeros(len(un_cur), np.uint8)
         status = status.reshape(-1).astype(np.uint8)
-        ef = c.f_threshold_edge_factor
-        if ef > 0.0 and F is not None and F.shape == (3, 3):
-            r_max = np.sqrt(cx * cx + cy * cy)
-            r_max_inv = 1.0 / r_max if r_max > 1e-6 else 0.0
-            f = F.astype(np.float64).ravel()
-            for i in range(len(status)):
-                if status[i]:
-                    continue
-                dx, dy = float(self.next_pts[i][0]) - cx, float(self.next_pts[i][1]) - cy
-                rr = np.sqrt(dx * dx + dy * dy) * r_max_inv
-                if rr < 0.3:
-                    continue
-                u1, v1 = float(un_cur[i][0]), float(un_cur[i][1])
-                u2, v2 = float(un_next[i][0]), float(un_next[i][1])
-                la = f[0] * u1 + f[1] * v1 + f[2]
-                lb = f[3] * u1 + f[4] * v1 + f[5]
-                lc = f[6] * u1 + f[7] * v1 + f[8]
-                nab = np.sqrt(la * la + lb * lb)
-                if nab < 1e-12:
-                    continue
-                dist = abs(la * u2 + lb * v2 + lc) / nab
-                if dist < c.f_threshold * (1.0 + ef * rr * rr):
-                    status[i] = 1
+        status = edge_recovery(status, F, un_cur, un_next, self.next_pts, c)
         self.stage["ransac_status"] = status.copy()
         self._filter(status)
 
@@ -290,6 +268,36 @@ class RefFeatureTracker:
                                     1.0, float(self.cur_pts[j][0]), float(self.cur_pts[j][1]),
                                     float(self.pts_velocity[j][0]), float(self.pts_velocity[j][1]))
         return out
+
+
+def edge_recovery(status, F, un_cur, un_next, next_pts, c: RefConfig) -> np.ndarray:
+    """ft:236-285 — distance-aware recovery of rejected edge features; returns the updated status (uint8)."""
+    status = np.array(status, np.uint8).reshape(-1)
+    cx, cy = c.col / 2.0, c.row / 2.0
+    ef = c.f_threshold_edge_factor
+    if ef > 0.0 and F is not None and np.asarray(F).shape == (3, 3):
+        r_max = np.sqrt(cx * cx + cy * cy)
+        r_max_inv = 1.0 / r_max if r_max > 1e-6 else 0.0
+        f = np.asarray(F, np.float64).ravel()
+        for i in range(len(status)):
+            if status[i]:
+                continue
+            dx, dy = float(next_pts[i][0]) - cx, float(next_pts[i][1]) - cy
+            rr = np.sqrt(dx * dx + dy * dy) * r_max_inv
+            if rr < 0.3:
+                continue
+            u1, v1 = float(un_cur[i][0]), float(un_cur[i][1])
+            u2, v2 = float(un_next[i][0]), float(un_next[i][1])
+            la = f[0] * u1 + f[1] * v1 + f[2]
+            lb = f[3] * u1 + f[4] * v1 + f[5]
+            lc = f[6] * u1 + f[7] * v1 + f[8]
+            nab = np.sqrt(la * la + lb * lb)
+            if nab < 1e-12:
+                continue
+            dist = abs(la * u2 + lb * v2 + lc) / nab
+            if dist < c.f_threshold * (1.0 + ef * rr * rr):
+                status[i] = 1
+    return status
 
 
 def config_from_synth(cfg: dict, **over) -> RefConfig:

@@ -146,36 +146,69 @@ __global__ void __launch_bounds__(32 * kPadWarps) pyr_pad_kernel(uint8_t* __rest
     pdl_entry();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t* sbase = pyr + (int64_t)blockIdx.y * pd.stream_bytes;
-    constexpr int NL = kPyrPadX / 4;
-#pragma unroll 1
-    for (int i = 0; i < kPadRowsPerWarp; ++i) {
-        int idx = (blockIdx.x * kPadWarps + warp) * kPadRowsPerWarp + i, l = 0;
+    constexpr int NL = kPyrPadX / 4, R = kPadRowsPerWarp;
+    // phase 1: locate the warp's rows and issue every load; phase 2: the stores (the rows are independent, so all of a
+    // warp's requests are in flight together instead of one row's round trip after the other)
+    uint8_t* drow[R];
+    const uint8_t* srow[R];
+    uint32_t v[R];
+    int x0[R], w[R];
+    bool outside[R];
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+        int idx = (blockIdx.x * kPadWarps + warp) * R + i, l = 0;
         for (; l < n_levels; ++l) {
             const int n = pd.lv[l].h + 2 * kPyrPadY;
             if (idx < n) break;
             idx -= n;
         }
-        if (l == n_levels) return;
+        x0[i] = 0x7fffffff;
+        outside[i] = false;
+        drow[i] = nullptr;
+        srow[i] = nullptr;
+        w[i] = 0;
+        v[i] = 0;
+        if (l == n_levels) continue;
         const LevelDesc L = pd.lv[l];
         const int y = idx - kPyrPadY;
-        const uint8_t* srow = sbase + L.offset + (int64_t)reflect101(y, L.h) * L.pitch;
-        uint8_t* drow = sbase + L.offset + (int64_t)y * L.pitch;
+        srow[i] = sbase + L.offset + (int64_t)reflect101(y, L.h) * L.pitch;
+        drow[i] = sbase + L.offset + (int64_t)y * L.pitch;
+        outside[i] = y < 0 || y >= L.h;
+        w[i] = L.w;
         const int xr0 = L.w & ~3, nright = (L.pitch - kPyrPadX - xr0) >> 2;
-        int x0 = 0x7fffffff;
-        if (lane < NL) x0 = -kPyrPadX + 4 * lane;
-        else if (lane - NL < nright) x0 = xr0 + 4 * (lane - NL);
-        if (x0 != 0x7fffffff) {
-            uint32_t v = 0;
+        if (lane < NL) x0[i] = -kPyrPadX + 4 * lane;
+        else if (lane - NL < nright) x0[i] = xr0 + 4 * (lane - NL);
+        if (x0[i] != 0x7fffffff) {
+            const int m = 2 * L.w - 2;                        // reflect101(x) = m - x right of the row, -x left of it
+            const int t = x0[i] < 0 ? -x0[i] : m - x0[i];     // source column of the word's FIRST byte; then t-1, t-2, t-3
+            if (L.w >= 64 && (x0[i] < 0 || x0[i] >= L.w)) {
+                // the four source bytes t-3 .. t sit in two aligned words: funnel-shift them together, then reverse
+                const int a = (t - 3) & ~3;
+                const uint32_t A = __ldg(reinterpret_cast<const uint32_t*>(srow[i] + a)), B = __ldg(reinterpret_cast<const uint32_t*>(srow[i] + a + 4));
+                v[i] = __byte_perm(__funnelshift_r(A, B, ((t - 3) & 3) * 8), 0, 0x0123);
+            } else {                                          // the word straddling the right edge, and tiny levels
 #pragma unroll
-            for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(srow + reflect101(x0 + b, L.w)) << (8 * b);   // in-range bytes map to themselves
-            *reinterpret_cast<uint32_t*>(drow + x0) = v;
+                for (int b = 0; b < 4; ++b) v[i] |= (uint32_t)__ldg(srow[i] + reflect101(x0[i] + b, L.w)) << (8 * b);
+            }
         }
-        if (y < 0 || y >= L.h) {
-            const int n16 = xr0 >> 4;
-            for (int c = lane; c < n16; c += 32) reinterpret_cast<uint4*>(drow)[c] = __ldg(reinterpret_cast<const uint4*>(srow) + c);
-            for (int c = (n16 << 2) + lane; c < (xr0 >> 2); c += 32)
-                reinterpret_cast<uint32_t*>(drow)[c] = __ldg(reinterpret_cast<const uint32_t*>(srow) + c);
+    }
+#pragma unroll
+    for (int i = 0; i < R; ++i)
+        if (x0[i] != 0x7fffffff) *reinterpret_cast<uint32_t*>(drow[i] + x0[i]) = v[i];
+    // rows above / below the level: 16-byte copies of the source row's interior
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+        if (!outside[i]) continue;                            // warp-uniform
+        const int xr0 = w[i] & ~3, n16 = xr0 >> 4;
+        for (int c = lane; c < n16; c += 64) {
+            const uint4 p0 = __ldg(reinterpret_cast<const uint4*>(srow[i]) + c);
+            const bool two = c + 32 < n16;
+            const uint4 p1 = two ? __ldg(reinterpret_cast<const uint4*>(srow[i]) + c + 32) : make_uint4(0, 0, 0, 0);
+            reinterpret_cast<uint4*>(drow[i])[c] = p0;
+            if (two) reinterpret_cast<uint4*>(drow[i])[c + 32] = p1;
         }
+        for (int c = (n16 << 2) + lane; c < (xr0 >> 2); c += 32)
+            reinterpret_cast<uint32_t*>(drow[i])[c] = __ldg(reinterpret_cast<const uint32_t*>(srow[i]) + c);
     }
 }
 

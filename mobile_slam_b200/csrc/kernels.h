@@ -22,7 +22,7 @@ void launch_copy_image(const uint8_t* src, int src_pitch, int64_t src_stride, ui
 void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from, int n_streams, cudaStream_t st,
                      int64_t* launches);
 
-// REFLECT_101 border (kPyrPadX / kPyrPadY) of levels 0 .. n_levels-1, one launch
+// REFLECT_101 border (kPyrPadX / kPyrPadY) of levels 0 .. n_levels-1, two launches (columns, then rows)
 void launch_pyr_pad(uint8_t* pyr_base, const PyrDesc& pd, int n_levels, int n_streams, cudaStream_t st, int64_t* launches);
 
 // ---- lk.cu (K9) ----

@@ -242,24 +242,43 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
     return d;
 }
 
-// Stage NROWS rows of 48 bytes of a level into the warp's tile; x0 is a multiple of 16.  Every level carries a REFLECT_101
-// border (kPyrPadX x kPyrPadY, written by pyr_pad_*_kernel), which covers every tile this kernel can ask for (origins
-// down to -48 columns / -26 rows, ends up to w + 42 / h + 26), so each 16-byte chunk goes global -> shared with ONE
-// asynchronous copy (cp.async.cg, 128 bits, no register staging, no border handling): 3 instructions per lane for a whole
-// search tile.  Pitches and level offsets are multiples of 16, so every chunk is 16-byte aligned on both sides.
-template <int NROWS>
-__device__ __forceinline__ void stage_rows16(uint32_t* tile, const uint8_t* __restrict__ img, int pitch, int x0, int y0, int lane) {
+// Stage NROWS rows of 48 bytes of a level into the warp's tile; x0 is a multiple of 16.  A 16-byte chunk goes global ->
+// shared with ONE asynchronous copy (cp.async.cg, 128 bits, no register staging): 3 instructions per lane for a whole
+// search tile.  Levels >= kPyrFirstPaddedLevel carry a REFLECT_101 border (kPyrPadX x kPyrPadY, pyr_pad_*_kernel) that
+// covers every tile this kernel can ask for (origins down to -48 columns / -26 rows, ends up to w + 42 / h + 26), so
+// there PADDED = true and no chunk needs border handling.  On the unpadded level 0 a chunk that is not fully inside the
+// level is assembled from REFLECT_101 bytes.  Pitches and level offsets are multiples of 16: chunks are aligned on both sides.
+template <int NROWS, bool PADDED>
+__device__ __forceinline__ void stage_rows16(uint32_t* tile, const uint8_t* __restrict__ img, int w, int h, int pitch,
+                                             int x0, int y0, int lane) {
     constexpr int CH = kFastPitch / 16, TOTAL = NROWS * CH, U = (TOTAL + 31) / 32;
     static_assert(kPyrPadX >= kFastPitch && kPyrPadY >= 21 + 1 + kLkMargin, "level border too small for the tiles");
     const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(tile);
-    const uint8_t* src = img + (int64_t)y0 * pitch + x0;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
         const int idx = lane + 32 * u;
         if (U * 32 != TOTAL && idx >= TOTAL) break;
         const int r = idx / CH, c = idx - r * CH;
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_s + (uint32_t)(r * kFastPitch + 16 * c)),
-                     "l"(src + (int64_t)r * pitch + 16 * c) : "memory");
+        const int gx = x0 + 16 * c, gy = y0 + r;
+        if (PADDED || (gy >= 0 && gy < h && gx >= 0 && gx + 16 <= w)) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_s + (uint32_t)(r * kFastPitch + 16 * c)),
+                         "l"(img + (int64_t)gy * pitch + gx) : "memory");
+        } else {
+            const uint8_t* row = img + (int64_t)reflect101(gy, h) * pitch;
+            uint32_t* dst = tile + r * (kFastPitch / 4) + 4 * c;
+#pragma unroll 1
+            for (int q = 0; q < 4; ++q) {
+                const int x = gx + 4 * q;
+                uint32_t v;
+                if (x >= 0 && x + 3 < w) {
+                    v = __ldg(reinterpret_cast<const uint32_t*>(row + x));
+                } else {
+                    v = (uint32_t)__ldg(row + reflect101(x, w)) | ((uint32_t)__ldg(row + reflect101(x + 1, w)) << 8) |
+                        ((uint32_t)__ldg(row + reflect101(x + 2, w)) << 16) | ((uint32_t)__ldg(row + reflect101(x + 3, w)) << 24);
+                }
+                dst[q] = v;
+            }
+        }
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
 }
@@ -322,7 +341,8 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
         // ---- template: tile origin (x aligned down to 16, ipy - 1), 24 rows x 48 bytes ----
         const int tx0 = (ipx - 1) & ~15, ax = (ipx - 1) - tx0;
         __syncwarp();
-        stage_rows16<WIN + 3>(tile, prev_base + L.offset, L.pitch, tx0, ipy - 1, lane);
+        if (level >= kPyrFirstPaddedLevel) stage_rows16<WIN + 3, true>(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, lane);
+        else stage_rows16<WIN + 3, false>(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, lane);
         __syncwarp();
         const bool border = ipx < 0 || ipy < 0 || ipx + WIN + 1 > L.w || ipy + WIN + 1 > L.h;
         int s11 = 0, s12 = 0, s22 = 0;
@@ -415,7 +435,8 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
                 tox = (iqx - kLkMargin) & ~15;
                 toy = iqy - kLkMargin;
                 __syncwarp();
-                stage_rows16<kFastRows>(tile, J, L.pitch, tox, toy, lane);
+                if (level >= kPyrFirstPaddedLevel) stage_rows16<kFastRows, true>(tile, J, L.w, L.h, L.pitch, tox, toy, lane);
+                else stage_rows16<kFastRows, false>(tile, J, L.w, L.h, L.pitch, tox, toy, lane);
                 __syncwarp();
                 staged = true;
             }

@@ -134,90 +134,74 @@ __global__ void __launch_bounds__(32 * kPdWarps) pyr_down_kernel(const uint8_t* 
     }
 }
 
-// ---- REFLECT_101 border of every built level (cv::buildOpticalFlowPyramid stores its levels padded the same way) -----
-// One launch for all levels: a warp takes kPadRowsPerWarp rows of the PADDED level (rows -kPyrPadY .. h + kPyrPadY - 1).
-// For every row it writes the column border — the 48 bytes left of the row and everything from the last aligned word of
-// the row to the end of the pitch, one aligned word per lane assembled from reflected bytes of source row
-// reflect101(y) — and, for the rows above / below the level, a 16-byte copy of that source row's interior.  Only border
-// bytes are written and only interior bytes are read, so no ordering between warps is needed.
-constexpr int kPadWarps = 8, kPadRowsPerWarp = 4;
+// ---- REFLECT_101 border of levels kPyrFirstPaddedLevel and up (cv::buildOpticalFlowPyramid stores its levels padded the same way) -----
+// One warp per row.  Columns first: the 48 bytes left of the row and everything from the last aligned word of the row to
+// the end of the pitch, one aligned word per lane: the four reflected source bytes t-3 .. t sit in two aligned words of the
+// row, which are funnel-shifted together and byte-reversed.  Then rows: pad row y is a 16-byte copy of the whole padded
+// row reflect101(y), corners included.
+// Measured alternatives (profiles/r2_experiments.json): one fused launch with 4 rows per warp (0.119 ms per C2 step
+// against 0.102 for these two launches) and padding inside the producers' CTAs (pyr_down with one CTA per row band +
+// clahe_apply, after a CTA barrier: 0.121 ms and +16 us single-stream latency).  The cost is that of ~600 K small,
+// scattered row-end writes per step, not of the re-read of rows that have left L2.
+constexpr int kPadWarps = 8;
 
-__global__ void __launch_bounds__(32 * kPadWarps) pyr_pad_kernel(uint8_t* __restrict__ pyr, PyrDesc pd, int n_levels) {
+__device__ __forceinline__ bool pad_locate(const PyrDesc& pd, int n_levels, int rows_of_level_extra, int idx, int& level, int& row) {
+    for (int l = kPyrFirstPaddedLevel; l < n_levels; ++l) {
+        const int n = rows_of_level_extra > 0 ? rows_of_level_extra : pd.lv[l].h;
+        if (idx < n) { level = l; row = idx; return true; }
+        idx -= n;
+    }
+    return false;
+}
+
+__global__ void __launch_bounds__(32 * kPadWarps) pyr_pad_x_kernel(uint8_t* __restrict__ pyr, PyrDesc pd, int n_levels) {
     pdl_entry();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint8_t* sbase = pyr + (int64_t)blockIdx.y * pd.stream_bytes;
-    constexpr int NL = kPyrPadX / 4, R = kPadRowsPerWarp;
-    // phase 1: locate the warp's rows and issue every load; phase 2: the stores (the rows are independent, so all of a
-    // warp's requests are in flight together instead of one row's round trip after the other)
-    uint8_t* drow[R];
-    const uint8_t* srow[R];
-    uint32_t v[R];
-    int x0[R], w[R];
-    bool outside[R];
+    int l, y;
+    if (!pad_locate(pd, n_levels, 0, blockIdx.x * kPadWarps + warp, l, y)) return;
+    const LevelDesc L = pd.lv[l];
+    uint8_t* row = pyr + (int64_t)blockIdx.y * pd.stream_bytes + L.offset + (int64_t)y * L.pitch;
+    constexpr int NL = kPyrPadX / 4;
+    const int xr0 = L.w & ~3, nright = (L.pitch - kPyrPadX - xr0) >> 2;
+    int x0;
+    if (lane < NL) x0 = -kPyrPadX + 4 * lane;
+    else if (lane - NL < nright) x0 = xr0 + 4 * (lane - NL);
+    else return;
+    const int t = x0 < 0 ? -x0 : 2 * L.w - 2 - x0;           // source column of the word's FIRST byte; then t-1, t-2, t-3
+    uint32_t v;
+    if (L.w >= 64 && (x0 < 0 || x0 >= L.w)) {
+        const int a = (t - 3) & ~3;
+        const uint32_t A = __ldg(reinterpret_cast<const uint32_t*>(row + a)), B = __ldg(reinterpret_cast<const uint32_t*>(row + a + 4));
+        v = __byte_perm(__funnelshift_r(A, B, ((t - 3) & 3) * 8), 0, 0x0123);
+    } else {                                                  // the word straddling the right edge, and tiny levels
+        v = 0;
 #pragma unroll
-    for (int i = 0; i < R; ++i) {
-        int idx = (blockIdx.x * kPadWarps + warp) * R + i, l = 0;
-        for (; l < n_levels; ++l) {
-            const int n = pd.lv[l].h + 2 * kPyrPadY;
-            if (idx < n) break;
-            idx -= n;
-        }
-        x0[i] = 0x7fffffff;
-        outside[i] = false;
-        drow[i] = nullptr;
-        srow[i] = nullptr;
-        w[i] = 0;
-        v[i] = 0;
-        if (l == n_levels) continue;
-        const LevelDesc L = pd.lv[l];
-        const int y = idx - kPyrPadY;
-        srow[i] = sbase + L.offset + (int64_t)reflect101(y, L.h) * L.pitch;
-        drow[i] = sbase + L.offset + (int64_t)y * L.pitch;
-        outside[i] = y < 0 || y >= L.h;
-        w[i] = L.w;
-        const int xr0 = L.w & ~3, nright = (L.pitch - kPyrPadX - xr0) >> 2;
-        if (lane < NL) x0[i] = -kPyrPadX + 4 * lane;
-        else if (lane - NL < nright) x0[i] = xr0 + 4 * (lane - NL);
-        if (x0[i] != 0x7fffffff) {
-            const int m = 2 * L.w - 2;                        // reflect101(x) = m - x right of the row, -x left of it
-            const int t = x0[i] < 0 ? -x0[i] : m - x0[i];     // source column of the word's FIRST byte; then t-1, t-2, t-3
-            if (L.w >= 64 && (x0[i] < 0 || x0[i] >= L.w)) {
-                // the four source bytes t-3 .. t sit in two aligned words: funnel-shift them together, then reverse
-                const int a = (t - 3) & ~3;
-                const uint32_t A = __ldg(reinterpret_cast<const uint32_t*>(srow[i] + a)), B = __ldg(reinterpret_cast<const uint32_t*>(srow[i] + a + 4));
-                v[i] = __byte_perm(__funnelshift_r(A, B, ((t - 3) & 3) * 8), 0, 0x0123);
-            } else {                                          // the word straddling the right edge, and tiny levels
-#pragma unroll
-                for (int b = 0; b < 4; ++b) v[i] |= (uint32_t)__ldg(srow[i] + reflect101(x0[i] + b, L.w)) << (8 * b);
-            }
-        }
+        for (int b = 0; b < 4; ++b) v |= (uint32_t)row[reflect101(x0 + b, L.w)] << (8 * b);     // in-range bytes map to themselves
     }
-#pragma unroll
-    for (int i = 0; i < R; ++i)
-        if (x0[i] != 0x7fffffff) *reinterpret_cast<uint32_t*>(drow[i] + x0[i]) = v[i];
-    // rows above / below the level: 16-byte copies of the source row's interior
-#pragma unroll
-    for (int i = 0; i < R; ++i) {
-        if (!outside[i]) continue;                            // warp-uniform
-        const int xr0 = w[i] & ~3, n16 = xr0 >> 4;
-        for (int c = lane; c < n16; c += 64) {
-            const uint4 p0 = __ldg(reinterpret_cast<const uint4*>(srow[i]) + c);
-            const bool two = c + 32 < n16;
-            const uint4 p1 = two ? __ldg(reinterpret_cast<const uint4*>(srow[i]) + c + 32) : make_uint4(0, 0, 0, 0);
-            reinterpret_cast<uint4*>(drow[i])[c] = p0;
-            if (two) reinterpret_cast<uint4*>(drow[i])[c + 32] = p1;
-        }
-        for (int c = (n16 << 2) + lane; c < (xr0 >> 2); c += 32)
-            reinterpret_cast<uint32_t*>(drow[i])[c] = __ldg(reinterpret_cast<const uint32_t*>(srow[i]) + c);
-    }
+    *reinterpret_cast<uint32_t*>(row + x0) = v;
+}
+
+__global__ void __launch_bounds__(32 * kPadWarps) pyr_pad_y_kernel(uint8_t* __restrict__ pyr, PyrDesc pd, int n_levels) {
+    pdl_entry();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int l, j;
+    if (!pad_locate(pd, n_levels, 2 * kPyrPadY, blockIdx.x * kPadWarps + warp, l, j)) return;
+    const LevelDesc L = pd.lv[l];
+    const int y = j < kPyrPadY ? j - kPyrPadY : L.h + (j - kPyrPadY);
+    uint8_t* base = pyr + (int64_t)blockIdx.y * pd.stream_bytes + L.offset - kPyrPadX;        // column -kPyrPadX of row 0
+    const uint4* src = reinterpret_cast<const uint4*>(base + (int64_t)reflect101(y, L.h) * L.pitch);
+    uint4* dst = reinterpret_cast<uint4*>(base + (int64_t)y * L.pitch);
+    for (int c = lane; c < (L.pitch >> 4); c += 32) dst[c] = src[c];
 }
 
 void launch_pyr_pad(uint8_t* pyr_base, const PyrDesc& pd, int n_levels, int n_streams, cudaStream_t st, int64_t* launches) {
     int rows = 0;
-    for (int l = 0; l < n_levels; ++l) rows += pd.lv[l].h + 2 * kPyrPadY;
-    const int per_cta = kPadWarps * kPadRowsPerWarp;
-    launch_pdl(pyr_pad_kernel, dim3((rows + per_cta - 1) / per_cta, n_streams), dim3(32 * kPadWarps), 0, st, pyr_base, pd, n_levels);
-    if (launches) *launches += 1;
+    for (int l = kPyrFirstPaddedLevel; l < n_levels; ++l) rows += pd.lv[l].h;
+    if (rows == 0) return;
+    launch_pdl(pyr_pad_x_kernel, dim3((rows + kPadWarps - 1) / kPadWarps, n_streams), dim3(32 * kPadWarps), 0, st, pyr_base, pd, n_levels);
+    launch_pdl(pyr_pad_y_kernel, dim3((2 * kPyrPadY * (n_levels - kPyrFirstPaddedLevel) + kPadWarps - 1) / kPadWarps, n_streams), dim3(32 * kPadWarps), 0, st,
+               pyr_base, pd, n_levels);
+    if (launches) *launches += 2;
 }
 
 void launch_pyr_down(const uint8_t* pyr_base, const PyrDesc& pd, int level_from, int n_streams, cudaStream_t st,

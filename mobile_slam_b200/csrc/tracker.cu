@@ -55,9 +55,10 @@ static void plan_pyramid(vs_tracker* t) {
     for (int l = 0; l < kMaxLevels; ++l) {
         pd.lv[l].w = w;
         pd.lv[l].h = h;
-        pd.lv[l].pitch = round_up(w + 2 * kPyrPadX, 16);
-        pd.lv[l].offset = off + (int64_t)kPyrPadY * pd.lv[l].pitch + kPyrPadX;      // pixel (0, 0) inside the padded block
-        off += (int64_t)round_up(pd.lv[l].pitch * (h + 2 * kPyrPadY), 256);
+        const int px = l >= kPyrFirstPaddedLevel ? kPyrPadX : 0, py = l >= kPyrFirstPaddedLevel ? kPyrPadY : 0;
+        pd.lv[l].pitch = round_up(w + 2 * px, 16);
+        pd.lv[l].offset = off + (int64_t)py * pd.lv[l].pitch + px;                  // pixel (0, 0) inside the padded block
+        off += (int64_t)round_up(pd.lv[l].pitch * (h + 2 * py), 256);
         w = (w + 1) / 2;
         h = (h + 1) / 2;
         if (w < 1) w = 1;

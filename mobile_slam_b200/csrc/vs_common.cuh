@@ -17,12 +17,17 @@ struct LevelDesc {
     int64_t offset;        // byte offset of the level inside one stream's pyramid block
 };
 
-// Every level is stored with a REFLECT_101 border of kPyrPadX columns / kPyrPadY rows (what cv::buildOpticalFlowPyramid
-// stores too): LevelDesc::offset addresses pixel (0, 0), rows -kPyrPadY .. h + kPyrPadY - 1 and columns -kPyrPadX ..
-// pitch - kPyrPadX - 1 exist.  The LK kernel's 48 x 32-byte search tiles (16-byte chunks, origin up to 48 columns / 26 rows
-// outside the level) then never need border handling.
+// Every level from kPyrFirstPaddedLevel up is stored with a REFLECT_101 border of kPyrPadX columns / kPyrPadY rows
+// (cv::buildOpticalFlowPyramid stores its levels padded too): LevelDesc::offset addresses pixel (0, 0), rows -kPyrPadY ..
+// h + kPyrPadY - 1 and columns -kPyrPadX .. pitch - kPyrPadX - 1 exist.  The LK kernel's 48 x 32-byte tiles (16-byte chunks,
+// origin up to 48 columns / 26 rows outside the level) then need no border handling, where on the coarse levels most tiles
+// cross the border.  kPyrFirstPaddedLevel = 1 (level 0 unpadded: it holds half of the border bytes while only ~12 % of its
+// tiles touch the border, LK assembles those chunks from reflected bytes) was measured too: border pass 0.102 -> 0.050 ms
+// but LK 0.591 -> 0.624 ms per C2 step and +7 us single-stream latency (profiles/r2_experiments.json) — a wash, so every
+// level is padded and the fast LK kernel carries no border path.
 constexpr int kPyrPadX = 48;       // multiple of 16
 constexpr int kPyrPadY = 32;
+constexpr int kPyrFirstPaddedLevel = 0;
 
 struct PyrDesc {
     int n_levels;          // levels actually built (<= maxLevel+1)

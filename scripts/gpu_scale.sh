@@ -7,6 +7,7 @@ RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-add
 [ "$N" = 1 ] && RUN="python"
 $RUN bench.py --gpus $N --config C5 --no-cpu > gpurun_out/${TAG}_bench_c5_n$N.json 2> gpurun_out/${TAG}_bench_c5_n$N.err; echo "c5 n=$N rc=$?"
 $RUN bench.py --gpus $N --no-cpu --no-c1 > gpurun_out/${TAG}_bench_c2_n$N.json 2> gpurun_out/${TAG}_bench_c2_n$N.err; echo "c2 n=$N rc=$?"
+python scripts/h2d_linkmap.py $N > gpurun_out/${TAG}_linkmap_n$N.json 2> gpurun_out/${TAG}_linkmap_n$N.err; echo "linkmap rc=$?"; cat gpurun_out/${TAG}_linkmap_n$N.json
 { nvidia-smi topo -m; echo; lscpu | grep -E "^CPU\(s\)|Model name|Socket|NUMA"; echo; lspci -tv 2>/dev/null | head -80; echo; free -g | head -2; } > gpurun_out/${TAG}_topo_n$N.txt 2>&1
 python - <<PY
 import json

@@ -11,7 +11,8 @@ public vectors), so a test can run both and the CUDA tracker on the same frames:
 
 What is NOT the reference here, and why: OpenCV itself is the cv2 4.13.0 wheel (the reference builds against an
 unpinned "OpenCV 4.x"); ``Eigen::EigenSolver`` in the Kannala-Brandt back-projection is LAPACK (numpy) behind a
-stand-in class (Eigen is absent); YAML loading is not built.  See oracle/ref_shim/ and oracle/Makefile.
+stand-in class (Eigen is absent); ``cv::FileStorage`` (camera YAML) is cv2.FileStorage.  See oracle/ref_shim/ and
+oracle/Makefile.
 
 Never imported by the product; bench.py may use it only in the CPU-baseline / ``--impl reference`` leg.
 """
@@ -45,6 +46,7 @@ class _Callbacks(C.Structure):
         ("find_f", C.CFUNCTYPE(C.c_int, _f32p, _f32p, C.c_int, C.c_int, C.c_double, C.c_double, _f64p, _u8p, _i32p)),
         ("circle", C.CFUNCTYPE(None, _u8p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)),
         ("imread_gray", C.CFUNCTYPE(None, C.c_char_p, _u8p, _i32p, _i32p)),
+        ("yaml_get", C.CFUNCTYPE(C.c_int, C.c_char_p, C.c_char_p, C.c_char_p, _f64p, C.POINTER(C.c_char), C.c_int)),
         ("eigvals", C.CFUNCTYPE(None, C.c_int, _f64p, _f64p, _f64p)),
     ]
 
@@ -176,6 +178,44 @@ def _cb_imread(path, out, rows, cols):
         np.ctypeslib.as_array(out, shape=im.shape)[:] = im
 
 
+_yaml_cache = {}
+
+
+@_guard
+def _cb_yaml_get(path, k1, k2, num, sbuf, cap):
+    """cv::FileStorage(path, READ)[k1][k2] answered by the real cv2.FileStorage"""
+    path, k1, k2 = path.decode(), k1.decode(), k2.decode()
+    fs = _yaml_cache.get(path)
+    if fs is None:
+        try:
+            fs = cv2.FileStorage(path, cv2.FILE_STORAGE_READ)
+        except cv2.error:
+            return -1
+        if not fs.isOpened():
+            return -1
+        _yaml_cache[path] = fs
+    if not k1:
+        return 0
+    node = fs.getNode(k1)
+    if k2:
+        if node.empty() or not node.isMap():
+            return 0
+        node = node.getNode(k2)
+    if node.empty() or node.isNone():
+        return 0
+    if node.isInt():
+        num[0] = float(int(node.real()))
+        return 1
+    if node.isReal():
+        num[0] = float(node.real())
+        return 2
+    if node.isString():
+        b = node.string().encode()[: cap - 1]
+        C.memmove(sbuf, b + b"\0", len(b) + 1)
+        return 3
+    return 0
+
+
 @_guard
 def _cb_eigvals(n, a, wr, wi):
     A = np.ctypeslib.as_array(a, shape=(n, n)).T.copy()     # column-major in, numpy is row-major
@@ -211,17 +251,46 @@ def load():
     lib.vsref_get_mask.argtypes = [C.c_void_p, C.c_void_p]
     lib.vsref_get_mask.restype = C.c_int
     lib.vsref_lift_projective.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    lib.vsref_read_intrinsic.argtypes = [C.c_void_p, C.c_char_p]
+    lib.vsref_read_intrinsic.restype = C.c_int
+    lib.vsref_camera_parameters.argtypes = [C.c_void_p, C.c_void_p, C.c_int, _i32p, _i32p]
+    lib.vsref_camera_parameters.restype = C.c_int
     lib.vsref_in_border.argtypes = [C.c_float, C.c_float]
     lib.vsref_in_border.restype = C.c_int
     cbs = _Callbacks()
     fns = dict(clahe_apply=_cb_clahe, lk=_cb_lk, gftt=_cb_gftt, find_f=_cb_find_f, circle=_cb_circle,
-               imread_gray=_cb_imread, eigvals=_cb_eigvals)
+               imread_gray=_cb_imread, yaml_get=_cb_yaml_get, eigvals=_cb_eigvals)
     for name, ctype in _Callbacks._fields_:
         setattr(cbs, name, ctype(fns[name]))
     _cb_keepalive = cbs
     lib.vsref_set_callbacks(C.byref(cbs))
     _lib = lib
     return lib
+
+
+def read_intrinsic_parameters(yaml_path: str):
+    """``FeatureTracker::readIntrinsicParameter`` of the compiled reference (CameraFactory::generateCameraFromYamlFile +
+    the model's Parameters::readFromYamlFile, cv::FileStorage served by cv2.FileStorage).  Returns
+    ``(model_type, width, height, parameter vector as Camera::writeParameters orders it)`` or ``None`` when the factory
+    returns a null camera (unknown model / unreadable file)."""
+    lib = load()
+    global _active, _cb_error
+    _active, _cb_error = None, None
+    _yaml_cache.pop(yaml_path, None)
+    h = lib.vsref_create()
+    try:
+        mt = lib.vsref_read_intrinsic(h, yaml_path.encode())
+        if _cb_error is not None:
+            e, _cb_error = _cb_error, None
+            raise e
+        if mt < 0:
+            return None
+        buf = np.zeros(64)
+        w, hh = C.c_int(0), C.c_int(0)
+        n = lib.vsref_camera_parameters(h, buf.ctypes.data, 64, C.byref(w), C.byref(hh))
+        return mt, w.value, hh.value, buf[:n].copy()
+    finally:
+        lib.vsref_destroy(h)
 
 
 class CompiledRefTracker:

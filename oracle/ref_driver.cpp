@@ -2,12 +2,13 @@
 //
 // Linked with (see oracle/Makefile, target `ref`):
 //   * /root/reference/src/frontend/feature_tracker.cpp                     — compiled where it lies, unmodified, whole;
-//   * oracle/_ref/gen/ref_cameras.cc                                        — the liftProjective-path functions of the
-//     reference's camera models, copied verbatim at build time by oracle/ref_extract.py (git-ignored output);
+//   * oracle/_ref/gen/ref_*.cc                                              — the liftProjective-path and YAML-loading functions
+//     of the reference's camera models and CameraFactory, copied verbatim at build time by oracle/ref_extract.py
+//     (git-ignored output, one unit per reference file);
 //   * the reference's own headers (include/frontend/feature_tracker.h, include/common/camera_models/*.h,
 //     include/utility/config.h) resolved against the Eigen / OpenCV / Ceres stand-ins in oracle/ref_shim/.
 // This file holds only what the link needs beyond that: the `utility::g_config` global, aborting stubs for the
-// virtuals of the camera classes that are NOT on the tracker's path (calibration, projection, YAML, undistortion
+// virtuals of the camera classes that are NOT on the tracker's path (calibration, projection, YAML writing, undistortion
 // maps — they need the real OpenCV/Eigen SDKs), and the `vsref_*` functions Python binds with ctypes
 // (oracle/ref_binding.py).  Never linked into, loaded by or shipped with the product.
 #include <cstdio>
@@ -20,7 +21,7 @@
 #include "common/camera_models/ScaramuzzaCamera.h"
 
 extern "C" {
-vs_ref_callbacks vs_ref_cb = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+vs_ref_callbacks vs_ref_cb = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 void (*vs_ref_eigvals_cb)(int, const double*, double*, double*) = nullptr;
 }
 
@@ -42,7 +43,6 @@ void Camera::estimateExtrinsics(const std::vector<cv::Point3f>&, const std::vect
 }
 
 #define VSREF_STUBS(CLS)                                                                                                \
-    bool CLS::Parameters::readFromYamlFile(const std::string&) { off_path(#CLS "::Parameters::readFromYamlFile"); }     \
     void CLS::Parameters::writeToYamlFile(const std::string&) const { off_path(#CLS "::Parameters::writeToYamlFile"); } \
     void CLS::estimateIntrinsics(const cv::Size&, const std::vector<std::vector<cv::Point3f>>&,                         \
                                  const std::vector<std::vector<cv::Point2f>>&) {                                        \
@@ -61,18 +61,9 @@ VSREF_STUBS(CataCamera)
 VSREF_STUBS(EquidistantCamera)
 VSREF_STUBS(OCAMCamera)
 
-// FeatureTracker::readIntrinsicParameter goes through the factory's YAML loader (cv::FileStorage): not built here.
-// The binding gives the tracker its camera through setIntrinsicParameter (the reference's own code) or m_camera.
+// CameraFactory::instance / generateCameraFromYamlFile and the cameras' readFromYamlFile come from the reference (generated
+// units); the static member's definition line is not a function body, so it is repeated here (CameraFactory.cc:27)
 std::shared_ptr<CameraFactory> CameraFactory::m_instance;
-CameraFactory::CameraFactory() {}
-std::shared_ptr<CameraFactory> CameraFactory::instance(void) {
-    if (!m_instance) m_instance.reset(new CameraFactory);
-    return m_instance;
-}
-CameraPtr CameraFactory::generateCameraFromYamlFile(const std::string& f) {
-    std::fprintf(stderr, "oracle/_ref: CameraFactory::generateCameraFromYamlFile(%s): YAML loading is not built here\n", f.c_str());
-    return CameraPtr();
-}
 
 }  // namespace camera_models
 }  // namespace common
@@ -147,6 +138,26 @@ void vsref_set_camera_ocam(void* h, int w, int hgt, double C, double D, double E
     p.center_y() = cy;
     for (int i = 0; i < SCARAMUZZA_POLY_SIZE; i++) p.poly(i) = poly5[i];
     ((FeatureTracker*)h)->m_camera = std::make_shared<OCAMCamera>(p);
+}
+
+// FeatureTracker::readIntrinsicParameter (feature_tracker.cpp:318-320) -> CameraFactory::generateCameraFromYamlFile
+// (CameraFactory.cc:87-150) -> <Model>::Parameters::readFromYamlFile, all reference code; cv::FileStorage is answered
+// by cv2.FileStorage.  Returns the model type, or -1 when the factory returned a null camera.
+int vsref_read_intrinsic(void* h, const char* yaml_path) {
+    FeatureTracker* ft = (FeatureTracker*)h;
+    ft->readIntrinsicParameter(yaml_path);
+    return ft->m_camera ? (int)ft->m_camera->modelType() : -1;
+}
+// the camera's parameter vector (Camera::writeParameters) and image size; returns the parameter count
+int vsref_camera_parameters(void* h, double* out, int cap, int* width, int* height) {
+    FeatureTracker* ft = (FeatureTracker*)h;
+    if (!ft->m_camera) return -1;
+    std::vector<double> p;
+    ft->m_camera->writeParameters(p);
+    for (int i = 0; i < (int)p.size() && i < cap; ++i) out[i] = p[i];
+    *width = ft->m_camera->imageWidth();
+    *height = ft->m_camera->imageHeight();
+    return (int)p.size();
 }
 
 // FeatureTracker::detectAndTrack on a caller-owned grey image (vio_engine.cpp:180 wraps the raw pointer the same way)

@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE ONLY — build step of oracle/_ref: copies selected FUNCTION DEFINITIONS, verbatim, out of the
-reference's camera-model sources (where they lie under /root/reference) into a generated translation unit under
-oracle/_ref/gen/ (git-ignored).  No reference source is stored in this repository.
+reference's camera-model sources (where they lie under /root/reference) into generated translation units under
+oracle/_ref/gen/ (git-ignored), one per reference file.  No reference source is stored in this repository.
 
 Why not compile the .cc files whole: besides ``liftProjective`` they hold calibration / undistortion-map /
 YAML code that needs the real OpenCV and Eigen SDKs (cv::FileStorage, cv::solvePnP, Eigen::JacobiSVD, …), absent
@@ -9,7 +9,7 @@ brace matching, so the recipe survives line shifts) and compiled against the ref
 stand-ins in oracle/ref_shim/.  The functions picked are listed in WANT below; every other virtual gets an aborting
 stub in oracle/ref_driver.cpp.
 
-usage: python oracle/ref_extract.py /root/reference oracle/_ref/gen/ref_cameras.cc
+usage: python oracle/ref_extract.py /root/reference oracle/_ref/gen
 """
 from __future__ import annotations
 
@@ -26,7 +26,14 @@ WANT = {
         r"Camera::Parameters::(modelType|cameraName|imageWidth|imageHeight|nIntrinsics)\(void\)",
         r"Camera::mask\(void\)",
     ],
+    "CameraFactory.cc": [
+        r"^bool iequals\(",
+        r"^CameraFactory::CameraFactory\(",
+        r"CameraFactory::instance\(void\)",
+        r"CameraFactory::generateCameraFromYamlFile\(",
+    ],
     "PinholeCamera.cc": [
+        r"PinholeCamera::Parameters::readFromYamlFile\(",
         r"^PinholeCamera::Parameters::Parameters\(",
         r"PinholeCamera::Parameters::(k1|k2|p1|p2|fx|fy|cx|cy)\(void\)",
         r"PinholeCamera::Parameters::operator=\(",
@@ -37,6 +44,7 @@ WANT = {
         r"PinholeCamera::(setParameters|readParameters|writeParameters)\(",
     ],
     "CataCamera.cc": [
+        r"CataCamera::Parameters::readFromYamlFile\(",
         r"^CataCamera::Parameters::Parameters\(",
         r"CataCamera::Parameters::(xi|k1|k2|p1|p2|gamma1|gamma2|u0|v0)\(void\)",
         r"CataCamera::Parameters::operator=\(",
@@ -47,6 +55,7 @@ WANT = {
         r"CataCamera::(setParameters|readParameters|writeParameters)\(",
     ],
     "EquidistantCamera.cc": [
+        r"EquidistantCamera::Parameters::readFromYamlFile\(",
         r"^EquidistantCamera::Parameters::Parameters\(",
         r"EquidistantCamera::Parameters::(k2|k3|k4|k5|mu|mv|u0|v0)\(void\)",
         r"EquidistantCamera::Parameters::operator=\(",
@@ -56,6 +65,8 @@ WANT = {
         r"EquidistantCamera::(setParameters|readParameters|writeParameters)\(",
     ],
     "ScaramuzzaCamera.cc": [
+        r"^bool iequals\(",
+        r"OCAMCamera::Parameters::readFromYamlFile\(",
         r"^OCAMCamera::Parameters::Parameters\(",
         r"OCAMCamera::Parameters::operator=\(",
         r"^OCAMCamera::OCAMCamera\(",
@@ -105,24 +116,32 @@ def definitions(text: str):
         i = j + 1
 
 
+HEADER = ["// GENERATED by oracle/ref_extract.py from the reference's sources — do not commit (oracle/_ref/ is git-ignored).",
+          "#include <algorithm>", "#include <cctype>", "#include <cmath>", "#include <cstring>", "#include <iostream>", "#include <string>",
+          "#include <vector>",
+          '#include "common/camera_models/Camera.h"', '#include "common/camera_models/PinholeCamera.h"',
+          '#include "common/camera_models/CataCamera.h"', '#include "common/camera_models/EquidistantCamera.h"',
+          '#include "common/camera_models/ScaramuzzaCamera.h"', '#include "common/camera_models/CameraFactory.h"',
+          "namespace common {", "namespace camera_models {", ""]
+
+
 def extract(ref_root: str):
-    out = ["// GENERATED by oracle/ref_extract.py from the reference's sources — do not commit (oracle/_ref/ is git-ignored).",
-           "#include <cstring>", "#include <cmath>", "#include <algorithm>", "#include <vector>",
-           '#include "common/camera_models/Camera.h"', '#include "common/camera_models/PinholeCamera.h"',
-           '#include "common/camera_models/CataCamera.h"', '#include "common/camera_models/EquidistantCamera.h"',
-           '#include "common/camera_models/ScaramuzzaCamera.h"', "namespace common {", "namespace camera_models {", ""]
-    manifest = []
+    """{reference file name: generated translation unit}, manifest lines.  One TU per reference file, as in the reference
+    (file-local helpers such as iequals() exist in more than one of them)."""
+    units, manifest = {}, []
     for fname, pats in WANT.items():
         path = os.path.join(ref_root, CAMERA_DIR, fname)
         text = open(path, encoding="utf-8").read()
         regs = [re.compile(p) for p in pats]
         hit = {p: 0 for p in pats}
+        out = list(HEADER)
         for line_no, sig, body in definitions(text):
-            # "^" patterns are constructors (no return type: the signature starts with the class name)
+            # "^" patterns match at the start of the signature (constructors and free helpers have no qualified return type)
             for p, r in zip(pats, regs):
                 if (r.match(sig) if p.startswith("^") else r.search(sig)):
                     out.append(f"// ---- {CAMERA_DIR}/{fname}:{line_no}")
-                    out.append(body)
+                    # a file-local helper (anonymous namespace in the reference) stays file-local here
+                    out.append("namespace {\n" + body + "\n}" if "::" not in sig.split("(")[0] else body)
                     out.append("")
                     manifest.append(f"{fname}:{line_no}-{line_no + body.count(chr(10))}  {sig.split('{')[0].strip()}")
                     hit[p] += 1
@@ -130,19 +149,24 @@ def extract(ref_root: str):
         missing = [p for p, c in hit.items() if c == 0]
         if missing:
             raise SystemExit(f"ref_extract: nothing in {fname} matches {missing}")
-    out += ["}  // namespace camera_models", "}  // namespace common", ""]
-    return "\n".join(out), manifest
+        out += ["}  // namespace camera_models", "}  // namespace common", ""]
+        units[fname] = "\n".join(out)
+    return units, manifest
 
 
 def main():
-    ref_root, dst = sys.argv[1], sys.argv[2]
-    src, manifest = extract(ref_root)
-    os.makedirs(os.path.dirname(dst), exist_ok=True)
-    with open(dst, "w", encoding="utf-8") as f:
-        f.write(src)
-    with open(os.path.splitext(dst)[0] + ".manifest.txt", "w", encoding="utf-8") as f:
+    ref_root, dst_dir = sys.argv[1], sys.argv[2]
+    units, manifest = extract(ref_root)
+    os.makedirs(dst_dir, exist_ok=True)
+    for f in os.listdir(dst_dir):
+        if f.startswith("ref_") and f.endswith(".cc"):
+            os.unlink(os.path.join(dst_dir, f))
+    for fname, src in units.items():
+        with open(os.path.join(dst_dir, "ref_" + fname), "w", encoding="utf-8") as f:
+            f.write(src)
+    with open(os.path.join(dst_dir, "manifest.txt"), "w", encoding="utf-8") as f:
         f.write("\n".join(manifest) + "\n")
-    print(f"ref_extract: {len(manifest)} definitions -> {dst}")
+    print(f"ref_extract: {len(manifest)} definitions -> {dst_dir}/ref_*.cc")
 
 
 if __name__ == "__main__":

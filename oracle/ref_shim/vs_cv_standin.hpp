@@ -276,6 +276,55 @@ inline Mat imread(const std::string& path, int /*flags*/ = IMREAD_GRAYSCALE) {
     return m;
 }
 
+// cv::FileStorage / cv::FileNode, read side only (CameraFactory::generateCameraFromYamlFile and the cameras'
+// Parameters::readFromYamlFile): every lookup is answered by the real cv2.FileStorage through vs_ref_cb.yaml_get
+class FileNode {
+public:
+    FileNode() {}
+    FileNode(const std::string& path, const std::string& k1, const std::string& k2) : path_(path), k1_(k1), k2_(k2) { fetch(); }
+    bool isNone() const { return kind_ <= 0; }
+    bool empty() const { return kind_ <= 0; }
+    FileNode operator[](const std::string& key) const { return k1_.empty() ? FileNode(path_, key, "") : FileNode(path_, k1_, key); }
+    FileNode operator[](const char* key) const { return (*this)[std::string(key)]; }
+    explicit operator int() const { return kind_ == 1 ? (int)num_ : kind_ == 2 ? cvRound(num_) : 0; }
+    explicit operator double() const { return (kind_ == 1 || kind_ == 2) ? num_ : 0.0; }
+    explicit operator float() const { return (float)(double)(*this); }
+    const std::string& str() const { return str_; }
+    int kind() const { return kind_; }
+
+private:
+    void fetch() {
+        vs_need((const void*)vs_ref_cb.yaml_get);
+        char buf[512];
+        buf[0] = 0;
+        kind_ = vs_ref_cb.yaml_get(path_.c_str(), k1_.c_str(), k2_.c_str(), &num_, buf, (int)sizeof(buf));
+        if (kind_ == 3) str_ = buf;
+    }
+    std::string path_, k1_, k2_, str_;
+    double num_ = 0.0;
+    int kind_ = 0;
+};
+inline void operator>>(const FileNode& n, std::string& out) { out = n.kind() == 3 ? n.str() : std::string(); }
+
+class FileStorage {
+public:
+    enum Mode { READ = 0, WRITE = 1 };
+    FileStorage(const std::string& path, int mode) : path_(path) {
+        vs_need((const void*)vs_ref_cb.yaml_get);
+        double d;
+        char b[8];
+        opened_ = mode == READ && vs_ref_cb.yaml_get(path.c_str(), "", "", &d, b, (int)sizeof(b)) >= 0;
+    }
+    bool isOpened() const { return opened_; }
+    FileNode operator[](const char* key) const { return FileNode(path_, key, ""); }
+    FileNode operator[](const std::string& key) const { return FileNode(path_, key, ""); }
+    void release() {}
+
+private:
+    std::string path_;
+    bool opened_ = false;
+};
+
 }  // namespace cv
 
 #endif

@@ -25,6 +25,10 @@ typedef struct vs_ref_callbacks {
     void (*circle)(unsigned char* img, long step, int rows, int cols, int cx, int cy, int radius, int color, int thickness);
     /* cv::imread(path, IMREAD_GRAYSCALE): call with out == NULL to get the size (0x0 when unreadable), then again */
     void (*imread_gray)(const char* path, unsigned char* out, int* rows, int* cols);
+    /* cv::FileStorage(path, READ)[k1][k2] (k2 = "" for a top-level key) through cv2.FileStorage: returns -1 when the file
+     * cannot be opened, 0 for a missing node, 1 for an integer node, 2 for a real node (value in *num), 3 for a string
+     * node (copied into str) */
+    int (*yaml_get)(const char* path, const char* k1, const char* k2, double* num, char* str, int str_cap);
     /* Eigen::EigenSolver stand-in: eigenvalues of an n x n column-major matrix (numpy.linalg.eigvals) */
     void (*eigvals)(int n, const double* a_colmajor, double* wr, double* wi);
 } vs_ref_callbacks;

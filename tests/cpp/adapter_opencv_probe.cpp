@@ -14,7 +14,7 @@
 
 namespace utility { Config g_config; }
 extern "C" {
-vs_ref_callbacks vs_ref_cb = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+vs_ref_callbacks vs_ref_cb = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 void (*vs_ref_eigvals_cb)(int, const double*, double*, double*) = nullptr;
 }
 

@@ -184,3 +184,150 @@ def test_other_camera_models_in_sequence(ref_lib):
                       affine=(1.0006, -2e-4, 3e-4))
     for c in (mei, sca):
         _run_pair(cfg, c, frames, [0.05 * k for k in range(6)])
+
+
+# ---- a13: readIntrinsicParameter (CameraFactory YAML route) of the compiled reference vs the product's readers ---------
+_YAMLS = {
+    "pinhole": """%YAML:1.0
+---
+model_type: PINHOLE
+camera_name: camera
+image_width: 752
+image_height: 480
+distortion_parameters:
+   k1: -2.917e-01
+   k2: 8.228e-02
+   p1: 5.333e-05
+   p2: -1.578e-04
+projection_parameters:
+   fx: 4.616e+02
+   fy: 4.603e+02
+   cx: 3.630e+02
+   cy: 2.481e+02
+""",
+    "kb": """%YAML:1.0
+---
+model_type: KANNALA_BRANDT
+camera_name: camera
+image_width: 512
+image_height: 512
+projection_parameters:
+   k2: 0.0034823894022493434
+   k3: 0.0007150348452162257
+   k4: -0.0020532361418706202
+   k5: 0.00020293673591811182
+   mu: 190.97847715128717
+   mv: 190.9733070521226
+   u0: 254.93170605935475
+   v0: 256.8974428996504
+""",
+    "mei": """%YAML:1.0
+---
+model_type: MEI
+camera_name: cam0
+image_width: 640
+image_height: 480
+mirror_parameters:
+   xi: 1.8
+distortion_parameters:
+   k1: -0.2
+   k2: 0.1
+   p1: 1.0e-04
+   p2: -2.0e-04
+projection_parameters:
+   gamma1: 700.5
+   gamma2: 705.25
+   u0: 320.5
+   v0: 239.75
+""",
+    "mei_default": """%YAML:1.0
+---
+camera_name: no_model_type_means_mei
+image_width: 640
+image_height: 480
+mirror_parameters:
+   xi: 0.9
+distortion_parameters:
+   k1: 0.
+   k2: 0.
+   p1: 0.
+   p2: 0.
+projection_parameters:
+   gamma1: 500.
+   gamma2: 500.
+   u0: 320.
+   v0: 240.
+""",
+    "scaramuzza": """%YAML:1.0
+---
+model_type: scaramuzza
+camera_name: ocam
+image_width: 752
+image_height: 480
+poly_parameters:
+   p0: -260.0
+   p1: 0.0
+   p2: 1.9e-03
+   p3: -2.0e-06
+   p4: 1.1e-08
+inv_poly_parameters:
+   p0: 380.0
+   p1: 210.0
+affine_parameters:
+   ac: 1.0006
+   ad: -2.0e-04
+   ae: 3.0e-04
+   cx: 376.2
+   cy: 239.7
+""",
+}
+
+
+def _product_vector(c):
+    """CameraParams -> the parameter vector in the order Camera::writeParameters uses for that model"""
+    from mobile_slam_b200 import _abi
+    if c.model_type == _abi.VS_CAM_PINHOLE or c.model_type == _abi.VS_CAM_KANNALA_BRANDT:
+        return list(c.d) + [c.fx, c.fy, c.cx, c.cy]
+    if c.model_type == _abi.VS_CAM_MEI:
+        return [c.xi] + list(c.d) + [c.fx, c.fy, c.cx, c.cy]
+    return list(c.affine) + [c.cx, c.cy] + list(c.poly)        # C, D, E, center_x, center_y, poly[5] (+ inv_poly, unused)
+
+
+@pytest.mark.parametrize("name", sorted(_YAMLS))
+def test_read_intrinsic_parameter_matches_compiled_reference(ref_lib, tmp_path, name):
+    from mobile_slam_b200.calib import camera_from_yaml
+    p = tmp_path / f"{name}.yaml"
+    p.write_text(_YAMLS[name])
+    ref = RB.read_intrinsic_parameters(str(p))
+    assert ref is not None
+    mt, w, h, vec = ref
+    c = camera_from_yaml(str(p))
+    assert (c.model_type, c.width, c.height) == (mt, w, h)
+    mine = _product_vector(c)
+    assert np.array_equal(np.asarray(mine, np.float64), vec[:len(mine)]), (mine, vec)
+
+
+def test_read_intrinsic_parameter_failures(ref_lib, tmp_path):
+    from mobile_slam_b200.calib import camera_from_yaml
+    bad = tmp_path / "bad.yaml"
+    bad.write_text("%YAML:1.0\n---\nmodel_type: FISHEYE_X\nimage_width: 10\nimage_height: 10\n")
+    assert RB.read_intrinsic_parameters(str(bad)) is None            # CameraFactory returns CameraPtr() (CameraFactory.cc:107-110)
+    with pytest.raises(ValueError):
+        camera_from_yaml(str(bad))
+    assert RB.read_intrinsic_parameters(str(tmp_path / "missing.yaml")) is None
+
+
+def test_reference_config_files(ref_lib):
+    """the reference's own calibration files, where the reference tree is present"""
+    import glob
+    from mobile_slam_b200.calib import camera_from_yaml
+    files = sorted(glob.glob("/root/reference/config/*.yaml"))
+    if not files:
+        pytest.skip("/root/reference/config absent")
+    for f in files:
+        ref = RB.read_intrinsic_parameters(f)
+        assert ref is not None, f
+        mt, w, h, vec = ref
+        c = camera_from_yaml(f)
+        mine = _product_vector(c)
+        assert (c.model_type, c.width, c.height) == (mt, w, h) and np.array_equal(np.asarray(mine, np.float64), vec[:len(mine)]), f

@@ -523,13 +523,22 @@ int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t s
     if (max_features <= 0 || p.n_levels <= 0) return 0;
     dim3 grid((max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta, n_streams);
     if (p.win == 21 && p.work_counters) {
-        static int resident = 0;
-        if (!resident) {
-            int dev = 0, sms = 148, per_sm = 2;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lk_fast21_kernel, 32 * kLkWarpsPerCta, 0);
-            resident = sms * (per_sm > 0 ? per_sm : 1);
+        // resident CTAs of the persistent kernel, per device (one process may drive several GPUs: vs::ShardedTracker)
+        static std::mutex mu;
+        static std::map<int, int> resident_of;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        int resident;
+        {
+            std::lock_guard<std::mutex> lock(mu);
+            int& r = resident_of[dev];
+            if (!r) {
+                int sms = 148, per_sm = 2;
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lk_fast21_kernel, 32 * kLkWarpsPerCta, 0);
+                r = sms * (per_sm > 0 ? per_sm : 1);
+            }
+            resident = r;
         }
         const int need = (n_streams * max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta;
         launch_pdl(lk_fast21_kernel, dim3(need < resident ? need : resident), dim3(32 * kLkWarpsPerCta), 0, st, p, n_streams, max_features,

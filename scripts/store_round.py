@@ -10,6 +10,7 @@ traffic = {"workload": f"C2 752x480, {streams} streams per launch, steady state 
            "source": f"ncu --set full --clock-control none, profiles/{tag}_ncu_<kernel>.txt: dram__bytes_read.sum + dram__bytes_write.sum per launch",
            "streams": streams, "kernels": {}}
 for k, name in [("lk_fast21", "lk"), ("shi_tomasi", "shi_tomasi"), ("clahe_lut", "clahe_lut"), ("clahe_apply", "clahe_apply"), ("pyr_down", "pyr_down"),
+                ("pyr_pad_x", "pyr_pad_x"), ("pyr_pad_y", "pyr_pad_y"),
                 ("post_lk_ransac_set_mask", "post_lk_ransac_set_mask"), ("select_finish", "select_finish")]:
     rep = os.path.join(go, f"{tag}_{k}_kernel.ncu-rep")
     if not os.path.exists(rep):

@@ -143,3 +143,17 @@ def test_adapter_opencv_mode_follows_g_config(tmp_path, built_lib):
             assert int(t[0]) == ft.ids[j] and int(t[3]) == ft.track_cnt[j]
             assert abs(float(t[1]) - ft.cur_pts[j][0]) < 1e-5 and abs(float(t[2]) - ft.cur_pts[j][1]) < 1e-5
     assert len(ft.ids) > 60          # max_cnt 80 took effect
+
+
+@pytest.mark.parametrize("defs", [["-DVS_WITH_OPENCV"], ["-DVS_WITH_REFERENCE_CONFIG"]])
+def test_adapter_single_macro_configurations_compile(tmp_path, defs):
+    """the two mixed build modes of the adapter header (OpenCV types with the per-instance config; g_config with the
+    library's own image / point types) at least type-check under -Wall -Werror"""
+    src = tmp_path / "t.cpp"
+    src.write_text('#include "vs_ref_callbacks.h"\n#include "utility/config.h"\n#include "vs_feature_tracker.hpp"\n'
+                   'namespace utility { Config g_config; }\n'
+                   'extern "C" { vs_ref_callbacks vs_ref_cb = {}; void (*vs_ref_eigvals_cb)(int, const double*, double*, double*) = nullptr; }\n'
+                   'int main() { frontend::FeatureTracker ft; (void)ft; return 0; }\n')
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", *defs, "-I", os.path.join(ROOT, "include"),
+                           "-I", os.path.join(ROOT, "oracle", "ref_shim"), "-I", os.path.join(ROOT, "tests", "cpp", "stubs"),
+                           "-c", str(src), "-o", str(tmp_path / "t.o")])

@@ -134,3 +134,39 @@ def test_sequence_with_cv_ransac_vs_compiled_reference(built_lib, ref_lib):
     assert exact >= int(0.85 * n_frames), f"{exact}/{n_frames} frames identical"
     bt.close()
     ref.close()
+
+
+def test_frontend_flags_mid_sequence_vs_compiled_reference(built_lib, ref_lib):
+    """g_config.feature_tracker.equalize / .fisheye and camera.focal_length are re-read by the reference inside every call
+    (feature_tracker.cpp:39-60,102,214-222): toggled between frames (vs_tracker_set_frontend_flags through the mirror's
+    per-call config), the CUDA tracker must keep following the compiled reference without losing its tracking state."""
+    cfg = dict(CONFIGS["C2"], width=376, height=240, max_cnt=100, min_dist=20, intr=(230.0, 230.0, 188.0, 120.0))
+    st = SynthStream(9, 376, 240, motion=1.5)
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    ft = FeatureTracker(tc)
+    ft.setCamera(cam)
+    rc = R.config_from_synth(cfg, use_ransac=False)
+    ref = RB.CompiledRefTracker(rc, ocam.from_config(cfg))
+    exact = 0
+    n_frames = 14
+    for k in range(n_frames):
+        if k == 3:
+            rc.fisheye = ft.config.fisheye = 1
+        if k == 6:
+            rc.equalize = ft.config.equalize = 0
+        if k == 9:
+            rc.fisheye = ft.config.fisheye = 0
+            rc.equalize = ft.config.equalize = 1
+        f = st.frame(k)
+        ft.detectAndTrack(f, 0.05 * k)
+        i = 0
+        while ft.updateID(i):
+            i += 1
+        ref.detect_and_track(f, 0.05 * k)
+        ref.update_all_ids()
+        assert len(ft.ids) > 40, f"frame {k}: tracking state lost ({len(ft.ids)} features)"
+        if ft.ids == ref.ids and ft.track_cnt == ref.track_cnt:
+            exact += 1
+            assert np.abs(ft.cur_pts - ref.cur_pts).max() <= 0.01
+    assert exact >= n_frames - 2, f"{exact}/{n_frames} frames identical in ids + track_cnt"
+    ref.close()

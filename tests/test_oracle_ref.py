@@ -173,6 +173,15 @@ def test_runtime_parameter_mutation(ref_lib):
             rc.max_cnt, rc.min_dist, rc.lk_window_size = 140, 10, 15
     _run_pair(cfg, ocam.from_config(cfg), frames, [0.05 * k for k in range(12)], mutate=mutate)
 
+    def flags(k, rc):                   # the fields the reference re-reads inside every call besides the mutators'
+        if k == 3:
+            rc.fisheye = 1              # the fisheye mask is built lazily on the first frame that has the flag (ft:39-60)
+        if k == 6:
+            rc.equalize = 0
+        if k == 8:
+            rc.fisheye, rc.equalize, rc.focal_length = 0, 1, 300.0
+    _run_pair(cfg, ocam.from_config(cfg), frames, [0.05 * k for k in range(12)], mutate=flags)
+
 
 def test_other_camera_models_in_sequence(ref_lib):
     """Mei and Scaramuzza cameras through the whole compiled tracker (undistorted points + velocity)."""

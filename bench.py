@@ -520,12 +520,11 @@ def measure(args, name, rank, world, local_rank, D, clocks, compact=False):
     if args.device_only:
         # profiling aid (ncu launch lists / captures of the device-resident pass alone): no e2e, latency or per-kernel legs
         bt.close()
+        total = D.sum(float(S * K))
         if rank == 0:
-            print(json.dumps({"metric": METRIC, "value": D.sum(float(S * K)) / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            print(json.dumps({"metric": METRIC, "value": total / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
                               "warmup": Wm, "ms_per_step": dev_ms / K, "gpu_launches": int(launches), "device_only": True,
                               "config": workload_config(args, cfg, S, name=name)}), flush=True)
-        else:
-            D.sum(0.0)
         return None
 
     # ---- (2) per-kernel CUDA events (profiling pass, same workload) ----

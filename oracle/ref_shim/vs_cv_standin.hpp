@@ -203,7 +203,7 @@ inline Ptr<CLAHE> createCLAHE(double clipLimit = 40.0, Size tileGridSize = Size(
 inline int buildOpticalFlowPyramid(const Mat& img, std::vector<Mat>& pyramid, Size /*winSize*/, int maxLevel,
                                    bool /*withDerivatives*/ = true) {
     pyramid.clear();
-    pyramid.push_back(img);
+    pyramid.push_back(img.clone());       // OpenCV copies the image into its padded level 0: the pyramid owns its pixels
     pyramid.back().pyr_levels = maxLevel;
     return maxLevel;
 }

@@ -68,7 +68,8 @@ def level_sizes(w, h, max_level, win=LK_WIN):
 
 def algorithmic_bytes(cfg, n_feat=None, win=LK_WIN):
     """Compulsory bytes per frame of each stage: CLAHE 3P, pyramid reads+writes,
-    Shi-Tomasi 2P, LK N(L+1)((w+3)^2+(w+1)^2), outputs 32N."""
+    Shi-Tomasi 2P, LK N(L+1)((w+3)^2+(w+1)^2), outputs 32N.  The REFLECT_101 border of the stored levels (kernel slot
+    "pyr_pad") is an implementation choice in the sense of §8d and has no algorithmic bytes: it shows in `kernels` only."""
     lv = level_sizes(cfg["width"], cfg["height"], cfg["max_level"], win)
     P = [a * b for a, b in lv]
     n = cfg["max_cnt"] if n_feat is None else n_feat

@@ -194,7 +194,7 @@ static inline bool direct_results(const vs_tracker* t) { return t->B <= kDirectR
 
 // ---- per-kernel CUDA-event profile (vs_tracker_set_profiling) ----
 static const char* const kProfNames[PK_COUNT] = {
-    "input_copy", "clahe_lut", "clahe_apply", "pyr_down", "lk", "lk_backward", "post_lk", "ransac",
+    "input_copy", "clahe_lut", "clahe_apply", "pyr_down", "pyr_pad", "lk", "lk_backward", "post_lk", "ransac",
     "set_mask", "shi_tomasi", "select_finish"};
 
 static void prof_begin(vs_tracker* t) {
@@ -570,8 +570,9 @@ static int build_pyramid(vs_tracker* t, int buf, const uint8_t* d_img, int pitch
     }
     const int nl = levels_to_build(t);
     for (int l = 0; l + 1 < nl; ++l) launch_pyr_down(t->d_pyr[buf], t->pd, l, t->B, t->stream, &t->launches);
-    launch_pyr_pad(t->d_pyr[buf], t->pd, nl, t->B, t->stream, &t->launches);
     prof_tick(t, PK_PYR_DOWN);
+    launch_pyr_pad(t->d_pyr[buf], t->pd, nl, t->B, t->stream, &t->launches);
+    prof_tick(t, PK_PYR_PAD);
     t->built[buf] = nl;
     return VS_OK;
 }

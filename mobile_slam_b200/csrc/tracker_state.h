@@ -8,7 +8,7 @@
 namespace vs {
 
 // kernel slots of the per-kernel CUDA-event profile (vs_tracker_get_profile)
-enum ProfSlot { PK_INPUT = 0, PK_CLAHE_LUT, PK_CLAHE_APPLY, PK_PYR_DOWN, PK_LK, PK_LK_BACK, PK_POST_LK, PK_RANSAC,
+enum ProfSlot { PK_INPUT = 0, PK_CLAHE_LUT, PK_CLAHE_APPLY, PK_PYR_DOWN, PK_PYR_PAD, PK_LK, PK_LK_BACK, PK_POST_LK, PK_RANSAC,
                 PK_SET_MASK, PK_SHI_TOMASI, PK_SELECT_FINISH, PK_COUNT };
 
 struct Profiler {

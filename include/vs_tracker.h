@@ -166,6 +166,10 @@ VS_API int vs_tracker_set_reject_callback(struct vs_tracker* t, vs_reject_fn fn,
 VS_API int vs_tracker_reset(struct vs_tracker* t, int32_t stream /* -1 = all */);
 /* number of CUDA kernels this handle has launched so far (bench.py "gpu_launches") */
 VS_API int64_t vs_tracker_launch_count(const struct vs_tracker* t);
+/* Debug aid: a handle created with VS_DEBUG_GUARD=1 in the environment brackets every device buffer with 4 KiB guard
+ * bands; this synchronises the device and returns how many guard bytes have been overwritten since creation
+ * (0 = clean, -1 = the handle was created without guards, -2 = CUDA error). */
+VS_API int64_t vs_tracker_debug_guard_check(struct vs_tracker* t);
 /* CUDA-event time (ms) of the device work of the last track call */
 VS_API float vs_tracker_last_device_ms(const struct vs_tracker* t);
 

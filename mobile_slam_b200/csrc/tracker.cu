@@ -402,6 +402,10 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     fill_camera(cfg->camera, g.cam);
     sync_glue_params(t);
     DeviceArena& A = t->arena;
+    {
+        const char* e = getenv("VS_DEBUG_GUARD");
+        A.guarded = e && atoi(e) != 0;
+    }
     VS_TRY_CREATE(A.alloc(&t->d_raw, (size_t)(B * t->raw_stride)));
     VS_TRY_CREATE(A.alloc(&t->d_pyr[0], (size_t)(B * t->pd.stream_bytes)));
     VS_TRY_CREATE(A.alloc(&t->d_pyr[1], (size_t)(B * t->pd.stream_bytes)));
@@ -1051,6 +1055,19 @@ int vs_tracker_reset(vs_tracker* t, int32_t stream) {
     }
     VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
     return VS_OK;
+}
+
+int64_t vs_tracker_debug_guard_check(vs_tracker* t) {
+    if (!t) return -2;
+    if (cudaSetDevice(t->cfg.device) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) return -2;
+    if (t->lanes.empty()) return t->arena.check();
+    int64_t bad = 0;
+    for (vs_tracker* l : t->lanes) {
+        const int64_t b = l->arena.check();
+        if (b < 0) return b;
+        bad += b;
+    }
+    return bad;
 }
 
 int64_t vs_tracker_launch_count(const vs_tracker* t) {

@@ -1,5 +1,6 @@
 // Handle state of the C ABI (include/vs_tracker.h) shared by tracker.cu and ransac.cu.
 #pragma once
+#include <cstdint>
 #include <vector>
 
 #include "../../include/vs_tracker.h"
@@ -21,22 +22,51 @@ struct Profiler {
 };
 
 struct DeviceArena {
-    std::vector<void*> blocks;
+    // Every block carries kSlack bytes after its payload: vector loads of the kernels may read (never write) a few bytes
+    // past the last element.  With VS_DEBUG_GUARD=1 in the environment at handle creation the block is additionally
+    // bracketed by two kGuard-byte bands of 0xA5 that nothing may write; check() counts the bytes that changed
+    // (compute-sanitizer is not available on every box — this is the repo's own out-of-bounds-write detector).
+    static constexpr size_t kSlack = 256, kGuard = 4096;
+    struct Block { void* base; size_t payload; };
+    std::vector<Block> blocks;
+    bool guarded = false;
     template <class T>
     cudaError_t alloc(T** p, size_t count, bool zero = true) {
+        const size_t payload = (count * sizeof(T) + 15) & ~(size_t)15;
+        const size_t lead = guarded ? kGuard : 0, tail = guarded ? kGuard : kSlack;
         void* q = nullptr;
-        cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 256);
+        cudaError_t e = cudaMalloc(&q, lead + payload + tail);
         if (e != cudaSuccess) return e;
-        blocks.push_back(q);
-        if (zero) {
-            e = cudaMemset(q, 0, count * sizeof(T) + 256);
+        blocks.push_back({q, payload});
+        uint8_t* b = static_cast<uint8_t*>(q);
+        if (guarded) {
+            e = cudaMemset(b, 0xA5, lead);
+            if (e == cudaSuccess) e = cudaMemset(b + lead + payload, 0xA5, tail);
             if (e != cudaSuccess) return e;
         }
-        *p = reinterpret_cast<T*>(q);
+        if (zero) {
+            e = cudaMemset(b + lead, 0, payload + (guarded ? 0 : tail));
+            if (e != cudaSuccess) return e;
+        }
+        *p = reinterpret_cast<T*>(b + lead);
         return cudaSuccess;
     }
+    // number of guard bytes that no longer hold 0xA5 (-1: guards were not enabled, -2: CUDA error)
+    int64_t check() const {
+        if (!guarded) return -1;
+        std::vector<uint8_t> h(kGuard);
+        int64_t bad = 0;
+        for (const Block& bk : blocks) {
+            const uint8_t* b = static_cast<const uint8_t*>(bk.base);
+            for (int side = 0; side < 2; ++side) {
+                if (cudaMemcpy(h.data(), b + (side ? kGuard + bk.payload : 0), kGuard, cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
+                for (uint8_t v : h) bad += v != 0xA5;
+            }
+        }
+        return bad;
+    }
     void release() {
-        for (void* b : blocks) cudaFree(b);
+        for (const Block& b : blocks) cudaFree(b.base);
         blocks.clear();
     }
 };

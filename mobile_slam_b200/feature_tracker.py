@@ -256,6 +256,10 @@ class BatchTracker:
     def reset(self, stream: int = -1):
         _abi.check(self._lib.vs_tracker_reset(self._h, stream))
 
+    def debug_guard_check(self) -> int:
+        """Overwritten guard bytes around the handle's device buffers (needs VS_DEBUG_GUARD=1 at creation; -1 without)."""
+        return int(self._lib.vs_tracker_debug_guard_check(self._h))
+
     @property
     def launch_count(self) -> int:
         return int(self._lib.vs_tracker_launch_count(self._h))

@@ -25,14 +25,15 @@ def _sequence(name, n_streams, n_frames, mode, lanes=0, fb=0, sizes=None):
         cfg.update(width=sizes[0], height=sizes[1], intr=(0.8 * sizes[0], 0.8 * sizes[0], sizes[0] / 2, sizes[1] / 2))
     tc, cam = config_from_synth(cfg, ransac_mode=mode, pipeline_lanes=lanes, fb_check=fb)
     t = BatchTracker(tc, cam, n_streams)
-    streams = [SynthStream(100 + s, cfg["width"], cfg["height"], motion=1.0 + 0.5 * (s % 3)) for s in range(n_streams)]
+    W, H = cfg["width"], cfg["height"]
+    streams = [SynthStream(100 + s, max(W, 256), max(H, 256), motion=1.0 + 0.5 * (s % 3)) for s in range(n_streams)]
     out = []
     for k in range(n_frames):
-        frames = [s.frame(k) for s in streams]
+        frames = [np.ascontiguousarray(s.frame(k)[:H, :W]) for s in streams]      # small sizes: a crop of a 256-px scene
         if n_streams > 2:                      # ragged: one blank stream, one scene cut
             frames[1] = np.zeros_like(frames[1])
             if k == 2:
-                frames[2] = streams[0].frame(40)
+                frames[2] = np.ascontiguousarray(streams[0].frame(40)[:H, :W])
         res = t.track(frames, [0.05 * k] * n_streams)
         out.append([(r.ids.copy(), r.cur_pts.copy(), r.track_cnt.copy(), r.cur_undistorted_pts.copy(), r.pts_velocity.copy()) for r in res])
     g = t.debug_guard_check()

@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstring>
 #include <deque>
+#include <exception>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -94,12 +95,13 @@ int decode_png(const uint8_t* d, int64_t n, uint8_t* out, int out_stride, int ma
     const bool depth_ok = (ctype == 0 && (depth == 1 || depth == 2 || depth == 4 || depth == 8 || depth == 16)) ||
                           (ctype == 3 && (depth == 1 || depth == 2 || depth == 4 || depth == 8)) ||
                           ((ctype == 2 || ctype == 4 || ctype == 6) && (depth == 8 || depth == 16));
-    if (!depth_ok || W == 0 || H == 0) { set_error("PNG: bad header (%ux%u, depth %d, type %d)", W, H, depth, ctype); return VS_ERR_INVALID; }
+    if (!depth_ok || W == 0 || H == 0 || W > 0x7fffffffu || H > 0x7fffffffu) { set_error("PNG: bad header (%ux%u, depth %d, type %d)", W, H, depth, ctype); return VS_ERR_INVALID; }
     if (interlace) { set_error("PNG: Adam7 interlacing is not supported"); return VS_ERR_INVALID; }
-    if ((int)W > max_w) { set_error("PNG is %u wide, the tracker expects at most %d", W, max_w); return VS_ERR_INVALID; }
+    if (W > (uint32_t)max_w) { set_error("PNG is %u wide, the tracker expects at most %d", W, max_w); return VS_ERR_INVALID; }
     *w_out = (int)W;
     *h_out = (int)H;
-    const int rows = (int)H < max_h ? (int)H : max_h;
+    const int rows = H < (uint32_t)max_h ? (int)H : max_h;
+    if (idat.size() > 0xffffffffull) { set_error("PNG: more than 4 GiB of image data"); return VS_ERR_INVALID; }
     const size_t rowbytes = ((size_t)W * channels * depth + 7) / 8;
     const int bpp = channels * depth >= 8 ? channels * depth / 8 : 1;
     std::vector<uint8_t> raw((rowbytes + 1) * (size_t)rows);
@@ -185,8 +187,8 @@ int decode_pgm(const uint8_t* d, int64_t n, uint8_t* out, int out_stride, int ma
         if (d[pos] == ' ' || d[pos] == '\t' || d[pos] == '\n' || d[pos] == '\r') { ++pos; continue; }
         int v = 0;
         bool any = false;
-        while (pos < n && d[pos] >= '0' && d[pos] <= '9') { v = v * 10 + (d[pos] - '0'); ++pos; any = true; }
-        if (!any) { set_error("PGM: bad header"); return VS_ERR_INVALID; }
+        while (pos < n && d[pos] >= '0' && d[pos] <= '9' && v < 100000000) { v = v * 10 + (d[pos] - '0'); ++pos; any = true; }
+        if (!any || v >= 100000000) { set_error("PGM: bad header"); return VS_ERR_INVALID; }
         vals[k++] = v;
     }
     if (k < 3 || pos >= n) { set_error("PGM: truncated header"); return VS_ERR_INVALID; }
@@ -209,7 +211,13 @@ int read_file(const char* path, std::vector<uint8_t>* buf) {
     const long sz = ftell(f);
     fseek(f, 0, SEEK_SET);
     if (sz <= 0) { fclose(f); set_error("Cannot load image: %s (empty)", path); return VS_ERR_INVALID; }
-    buf->resize((size_t)sz);
+    try {
+        buf->resize((size_t)sz);
+    } catch (const std::exception&) {
+        fclose(f);
+        set_error("Cannot load image: %s (%ld bytes do not fit in memory)", path, sz);
+        return VS_ERR_NOMEM;
+    }
     const size_t got = fread(buf->data(), 1, (size_t)sz, f);
     fclose(f);
     if (got != (size_t)sz) { set_error("Cannot load image: %s (short read)", path); return VS_ERR_INVALID; }
@@ -377,8 +385,13 @@ extern "C" {
 int vs_image_decode_gray(const uint8_t* bytes, int64_t n, uint8_t* out, int32_t out_stride, int32_t max_w, int32_t max_h,
                          int32_t* w, int32_t* h) {
     if (!bytes || !out || !w || !h || n < 4 || out_stride < max_w || max_w <= 0 || max_h <= 0) { set_error("vs_image_decode_gray: bad argument"); return VS_ERR_INVALID; }
-    if (bytes[0] == 0x89 && bytes[1] == 'P') return decode_png(bytes, n, out, out_stride, max_w, max_h, w, h);
-    if (bytes[0] == 'P' && bytes[1] == '5') return decode_pgm(bytes, n, out, out_stride, max_w, max_h, w, h);
+    try {                                       // nothing may unwind through the C boundary (std::vector growth)
+        if (bytes[0] == 0x89 && bytes[1] == 'P') return decode_png(bytes, n, out, out_stride, max_w, max_h, w, h);
+        if (bytes[0] == 'P' && bytes[1] == '5') return decode_pgm(bytes, n, out, out_stride, max_w, max_h, w, h);
+    } catch (const std::exception& e) {
+        set_error("image decode: %s", e.what());
+        return VS_ERR_NOMEM;
+    }
     set_error("unsupported image format (PNG and binary PGM are)");
     return VS_ERR_INVALID;
 }
@@ -386,7 +399,13 @@ int vs_image_decode_gray(const uint8_t* bytes, int64_t n, uint8_t* out, int32_t 
 int vs_image_read_gray(const char* path, uint8_t* out, int32_t out_stride, int32_t max_w, int32_t max_h, int32_t* w, int32_t* h) {
     if (!path) { set_error("vs_image_read_gray: null path"); return VS_ERR_INVALID; }
     std::vector<uint8_t> buf;
-    const int rc = read_file(path, &buf);
+    int rc;
+    try {
+        rc = read_file(path, &buf);
+    } catch (const std::exception& e) {
+        set_error("Cannot load image: %s (%s)", path, e.what());
+        return VS_ERR_NOMEM;
+    }
     if (rc != VS_OK) return rc;
     return vs_image_decode_gray(buf.data(), (int64_t)buf.size(), out, out_stride, max_w, max_h, w, h);
 }

@@ -210,3 +210,66 @@ def test_files_on_disk_to_published_records(tmp_path, built_lib):
         pipe.wait()                                         # nothing outstanding
     pipe.close()
     bt.close()
+
+
+def _fuzz_child(n_cases):
+    """mutated PNG / PGM streams through vs_image_decode_gray: every call must RETURN (image or VsError)"""
+    import ctypes as C
+    from mobile_slam_b200 import VsError, _abi
+    rng = np.random.default_rng(12345)
+    img = rng.integers(0, 256, (37, 53), dtype=np.uint8)
+    seeds = [cv2.imencode(".png", img)[1].tobytes(),
+             cv2.imencode(".png", np.dstack([img, img[::-1], img.T[:37, :37].repeat(2, 1)[:, :53]]))[1].tobytes(),
+             cv2.imencode(".png", (img.astype(np.uint16) << 8) | 7)[1].tobytes(),
+             _png(9, 5, 2, 3, [rng.integers(0, 256, 3, dtype=np.uint8)] * 5, palette=rng.integers(0, 256, (4, 3))),
+             cv2.imencode(".pgm", img)[1].tobytes()]
+    lib = _abi.load()
+    out = np.zeros((64, 64), np.uint8)
+    w, h = C.c_int32(0), C.c_int32(0)
+    ok = bad = 0
+
+    def feed(data):
+        nonlocal ok, bad
+        buf = (C.c_ubyte * max(len(data), 1)).from_buffer_copy(data.ljust(1, b"\0"))
+        rc = lib.vs_image_decode_gray(buf, len(data), out.ctypes.data, 64, 64, 64, C.byref(w), C.byref(h))
+        ok, bad = ok + (rc == 0), bad + (rc != 0)
+
+    # crafted headers first: sizes that overflow int / size_t arithmetic, zero sizes, absurd chunk lengths
+    base = seeds[0]
+    for wv, hv in ((0xFFFFFFFF, 1), (1, 0xFFFFFFFF), (0x7FFFFFFF, 0x7FFFFFFF), (0, 5), (5, 0), (64, 0x80000000), (0x80000001, 3)):
+        hdr = struct.pack(">IIBBBBB", wv, hv, 8, 0, 0, 0, 0)
+        feed(base[:16] + hdr + struct.pack(">I", zlib.crc32(b"IHDR" + hdr) & 0xffffffff) + base[33:])
+    feed(base[:33] + struct.pack(">I", 0xFFFFFFF0) + base[37:])
+    feed(base[:33] + struct.pack(">I", 0x7FFFFFFF) + base[37:])
+    for hdr in (b"P5\n99999999999999999999 3\n255\n", b"P5\n3 99999999999\n255\n", b"P5\n2147483647 2147483647\n255\nxx",
+                b"P5\n-3 4\n255\n", b"P5\n3 4\n65535\n" + b"\0" * 24, b"P5\n# only a comment", b"P5", b"P5\n3 4\n255"):
+        feed(hdr)
+    assert ok == 0, "a crafted header decoded"
+    for k in range(n_cases):
+        d = bytearray(seeds[k % len(seeds)])
+        kind = rng.integers(0, 4)
+        if kind == 0:                                    # byte flips
+            for _ in range(int(rng.integers(1, 6))):
+                d[int(rng.integers(0, len(d)))] = int(rng.integers(0, 256))
+        elif kind == 1:                                  # truncation
+            d = d[: int(rng.integers(0, len(d)))]
+        elif kind == 2:                                  # a random 32-bit field (lengths, sizes) replaced by an extreme
+            i = int(rng.integers(0, max(len(d) - 4, 1)))
+            d[i:i + 4] = struct.pack(">I", int(rng.choice([0, 1, 0x7FFFFFFF, 0x80000000, 0xFFFFFFFF, 0xFFFF])))
+        else:                                            # a slice duplicated / dropped
+            i, j = sorted(int(x) for x in rng.integers(0, len(d), 2))
+            d = d[:i] + d[j:] if rng.integers(0, 2) else d[:j] + d[i:j] + d[j:]
+        feed(bytes(d))
+    print(f"fuzz ok decoded={ok} rejected={bad}")
+
+
+def test_decoder_survives_malformed_streams():
+    """a decoder that reads files from disk must reject damage, never crash or balloon: crafted IHDR / PGM sizes that
+    overflow 32-bit arithmetic, absurd chunk lengths, truncations and random mutations, in a child process"""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = f"import sys; sys.path.insert(0, {root!r}); sys.path.insert(0, {os.path.join(root, 'tests')!r}); " \
+           f"import test_ingest as T; T._fuzz_child(4000)"
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root)
+    assert r.returncode == 0 and "fuzz ok" in r.stdout, (r.returncode, r.stdout[-500:], r.stderr[-2000:])

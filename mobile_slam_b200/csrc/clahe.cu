@@ -5,6 +5,7 @@
 #include <cuda_fp16.h>
 
 #include <cmath>
+#include <type_traits>
 
 #include "kernels.h"
 
@@ -20,12 +21,23 @@ namespace vs {
 // picks the CTA size from the tile area), so the byte counters cannot overflow.  The private
 // counters are then summed with packed 16-bit adds.
 // ---------------------------------------------------------------------------------------------
+// v >> s (0 < s < 32) as mul.hi(v, 2^(32 - s)): same value, issued to the multiplier pipe instead of the shifter
+__device__ __forceinline__ uint32_t shr_mul(uint32_t v, int s) {
+    if (s == 0) return v;
+    uint32_t d;
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(d) : "r"(v), "r"(1u << (32 - s)));
+    return d;
+}
+
 template <int NT, bool FULLW>
 __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict__ src, int pitch, int64_t img_stride,
                                                        int tw, int th, int clip, float lut_scale,
                                                        uint8_t* __restrict__ luts) {
     pdl_entry();
-    extern __shared__ __align__(16) uint32_t s_cnt[];          // [64 word rows][NT threads]
+    // [64 word rows][NT threads]; static up to 32 KB so its address is an immediate of the shared atomics below
+    extern __shared__ __align__(16) uint32_t s_cnt_dyn[];
+    __shared__ __align__(16) uint32_t s_cnt_static[NT <= 128 ? 64 * NT : 4];
+    uint32_t* const s_cnt = NT <= 128 ? s_cnt_static : s_cnt_dyn;
     __shared__ uint32_t s_part[NT >= 64 ? NT / 64 : 1][64][2];
     __shared__ int s_hist[256];
     __shared__ unsigned int s_warp_tot[NT / 32];
@@ -42,28 +54,31 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict
     // aligned words covering the tile's columns [x0, x0 + tw); the first / last word may be partial
     const int x0 = tx * tw, y0 = ty * th;
     const int xa = x0 & ~3, nw = ((x0 + tw - 1) >> 2) - (xa >> 2) + 1;
-    uint32_t* mine = s_cnt + tid;
+    const uint32_t tid4 = 4u * (uint32_t)tid;
     // thread walks the tile's words in row-major order, NT apart: (y, q) advance incrementally
     const int dq = NT % nw, dy = NT / nw;
-    int y = tid / nw, q = tid - y * nw;
-    const uint8_t* rowp = img + (int64_t)(y0 + y) * pitch + xa;
-    while (y < th) {
-        // up to four independent loads in flight per thread before the dependent shared-memory updates
+    const int yt = tid / nw;
+    int q = tid - yt * nw;
+    const uint8_t* rowp = img + (int64_t)(y0 + yt) * pitch + xa;
+    // a thread's words come in trips of four (four independent loads in flight before the dependent shared-memory
+    // updates); only the last trip can hold past-the-end slots, so the full trips carry no validity test at all
+    const int total_words = nw * th;
+    const int n_mine = tid < total_words ? (total_words - tid + NT - 1) / NT : 0;
+    auto trip = [&](auto tail_tag, int n_valid) {
+        constexpr bool TAIL = decltype(tail_tag)::value;
         uint32_t v[4];
         int lo[4], hi[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const bool ok = y < th;
+            const bool ok = !TAIL || u < n_valid;
             v[u] = ok ? __ldg(reinterpret_cast<const uint32_t*>(rowp) + q) : 0u;
             const int xw = xa + 4 * q;
             lo[u] = ok ? max(x0 - xw, 0) : 4;              // valid bytes of this word: lo .. hi-1
             hi[u] = min(x0 + tw - xw, 4);
             q += dq;
-            y += dy;
             rowp += (int64_t)dy * pitch;
             if (q >= nw) {
                 q -= nw;
-                ++y;
                 rowp += pitch;
             }
         }
@@ -71,14 +86,25 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(const uint8_t* __restrict
         for (int u = 0; u < 4; ++u) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const uint32_t b = (v[u] >> (8 * k)) & 255u;
-                // FULLW: every tile starts on a word boundary and is a whole number of words wide, so only the
-                // past-the-end slots of the last trip (lo = 4) are invalid: one test per word instead of two per pixel
-                const uint32_t inc = (FULLW ? lo[u] == 0 : (k >= lo[u] && k < hi[u])) ? (1u << ((b >> 3) & 0x18u)) : 0u;
-                atomicAdd(&mine[(b & 63u) * NT], inc);      // ATOMS without a result: one instruction, no load-add-store chain
+                // FULLW: every tile starts on a word boundary and is a whole number of words wide: every byte of a valid
+                // word counts
+                const bool valid = FULLW ? (!TAIL || lo[u] == 0) : (k >= lo[u] && k < hi[u]);
+                // The loop is bound by the integer-ALU pipe (shifts, logic), the multiplier pipe idles: right shifts are
+                // therefore taken as the high half of a multiplication by a power of two (mul.hi on the FMA pipe).
+                // byte lane of bin b = b >> 6: the counter increment is 1 << 8 * (b >> 6)
+                const uint32_t inc = valid ? (1u << (shr_mul(v[u], 8 * k + 3) & 0x18u)) : 0u;
+                // byte offset of word row (b & 63) in this thread's column, taken straight from the pixel word: one
+                // shift + one mask-or per pixel (NT * 4 is a power of two)
+                constexpr int SH = (NT == 32 ? 7 : NT == 64 ? 8 : NT == 128 ? 9 : 10);     // log2(NT * 4)
+                const uint32_t off = ((8 * k >= SH ? shr_mul(v[u], 8 * k - SH) : v[u] << (SH - 8 * k)) & (63u << SH)) | tid4;
+                // ATOMS without a result: one instruction, no load-add-store chain
+                atomicAdd(reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(s_cnt) + off), inc);
             }
         }
-    }
+    };
+#pragma unroll 1
+    for (int t4 = 0; t4 < (n_mine >> 2); ++t4) trip(std::false_type{}, 4);
+    if (n_mine & 3) trip(std::true_type{}, n_mine & 3);
     __syncthreads();
     // sum the NT private copies (packed 16-bit sums of bytes (0, 2) and (1, 3)), rotated so lanes hit distinct banks
     if constexpr (NT == 32) {
@@ -373,11 +399,16 @@ __global__ void __launch_bounds__(1024) clahe_apply_kernel(const uint8_t* __rest
             else
                 for (int k = 0; k < 8 && x + k < W; ++k) dp[k] = (uint8_t)(o[k >> 2] >> (8 * (k & 3)));
         };
-        for (int y = y_begin + 2 * rg; y < y_end; y += 2 * rgroups) {
-            // two rows (16 pixels) in flight per lane before the dependent table lookups
-            const uint2 a0 = fetch(y), a1 = fetch(y + 1);
+        // two rows (16 pixels) per trip; the NEXT trip's rows are requested before this trip's table lookups, so the
+        // global-load latency is covered by a whole trip of arithmetic instead of being waited out at its start
+        int y = y_begin + 2 * rg;
+        uint2 a0 = fetch(y), a1 = fetch(y + 1);
+        for (; y < y_end; y += 2 * rgroups) {
+            const uint2 n0 = fetch(y + 2 * rgroups), n1 = fetch(y + 2 * rgroups + 1);
             process(y, a0);
             process(y + 1, a1);
+            a0 = n0;
+            a1 = n1;
         }
     }   // chunk
 }
@@ -423,7 +454,7 @@ static ClaheGeom clahe_geom(int W, int H) {
 template <int NT, bool FULLW>
 static void launch_lut_nt2(const uint8_t* src, int src_pitch, int64_t src_stride, const ClaheGeom& g, int n_streams,
                            uint8_t* luts, cudaStream_t st) {
-    const int smem = 64 * NT * 4;
+    const int smem = NT <= 128 ? 0 : 64 * NT * 4;
     ensure_dyn_smem(reinterpret_cast<const void*>(clahe_lut_kernel<NT, FULLW>), smem);
     launch_pdl(clahe_lut_kernel<NT, FULLW>, dim3(kClaheTiles * kClaheTiles, n_streams), dim3(NT), smem, st,
         src, src_pitch, src_stride, g.tw, g.th, g.clip, g.lut_scale, luts);

@@ -90,6 +90,41 @@ def test_pyramid_bit_exact(trackers, name):
         assert np.array_equal(a, b), f"level {l}: {np.count_nonzero(a != b)} pixels differ"
 
 
+@pytest.mark.parametrize("w0", [88, 97, 100, 135])
+def test_pyramid_every_width_residue(built_lib, w0):
+    """the right border is patched in registers with one byte permutation per (source width mod 8): widths w0 .. w0 + 8
+    put every residue on every level; heights odd and even; random pixels so a wrong border byte cannot hide"""
+    rng = np.random.default_rng(w0)
+    for w in range(w0, w0 + 9):
+        h = 90 + (w % 5)
+        cfg = dict(ODD, width=w, height=h, intr=(80.0, 80.0, w / 2, h / 2))
+        tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+        bt = BatchTracker(tc, cam, 1)
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        got = bt.stage_pyramid(img)
+        _, pyr = cv2.buildOpticalFlowPyramid(img, (21, 21), 3, withDerivatives=False)
+        assert len(got) == len(pyr)
+        for l, (a, b) in enumerate(zip(got, pyr)):
+            assert np.array_equal(a, b), f"{w}x{h} level {l}: {np.count_nonzero(a != b)} pixels differ"
+        bt.close()
+
+
+def test_pyramid_narrow_levels(built_lib):
+    """a small LK window lets the pyramid go down to levels narrower than 16 pixels (one-thread-per-pixel kernel)"""
+    rng = np.random.default_rng(5)
+    for w, h in ((40, 36), (59, 60), (33, 64)):
+        cfg = dict(ODD, width=w, height=h, intr=(40.0, 40.0, w / 2, h / 2), max_level=4)
+        tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF, lk_window_size=5)
+        bt = BatchTracker(tc, cam, 1)
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        got = bt.stage_pyramid(img)
+        _, pyr = cv2.buildOpticalFlowPyramid(img, (5, 5), 4, withDerivatives=False)
+        assert len(got) == len(pyr) and min(a.shape[1] for a in got) < 16
+        for l, (a, b) in enumerate(zip(got, pyr)):
+            assert np.array_equal(a, b), f"{w}x{h} level {l}: {np.count_nonzero(a != b)} pixels differ"
+        bt.close()
+
+
 def test_pyramid_stops_when_level_not_larger_than_window(trackers):
     # 100x100, win 21, maxLevel 3 -> only levels 0..2 (SURVEY.md S2)
     cfg = dict(ODD, width=100, height=100)

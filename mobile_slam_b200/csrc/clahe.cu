@@ -5,6 +5,7 @@
 #include <cuda_fp16.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <type_traits>
 
 #include "kernels.h"
@@ -285,7 +286,8 @@ __global__ void __launch_bounds__(256) clahe_lut_generic_kernel(const uint8_t* _
 // held in registers.
 // ---------------------------------------------------------------------------------------------
 constexpr int kApplyCells = kClaheTiles + 1;   // interpolation cells per row: cx = -1 .. 7
-constexpr int kApplyRowSplit = 2;             // CTAs per band (each rebuilds the band's cell tables)
+// CTAs per band (each rebuilds the band's cell tables): chosen by the launcher — 1 when the batch alone fills the GPU
+// (the table build is ~10 % of a CTA's instructions), more with few streams so that enough CTAs exist
 
 struct ClaheBands {
     int start[kClaheTiles + 2];   // band b (cell row b-1) covers rows start[b] .. start[b+1]-1
@@ -305,15 +307,15 @@ __global__ void __launch_bounds__(1024) clahe_apply_kernel(const uint8_t* __rest
                                                            int64_t src_stride, uint8_t* __restrict__ dst,
                                                            int dst_pitch, int64_t dst_stride, int W, int H,
                                                            float inv_tw, float inv_th, ClaheBands bands,
-                                                           const uint8_t* __restrict__ luts) {
+                                                           const uint8_t* __restrict__ luts, int row_split) {
     pdl_entry();
     __shared__ __align__(16) uint2 s_cell[kApplyCells][256];         // (p1, p2 | q1, q2) as 4 x fp16 (bytes are exact in fp16)
     __shared__ float2 s_ya[kApplyMaxBandRows];                        // (ya1, ya) of the CTA's rows
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int s = blockIdx.y;
-    const int band = blockIdx.x / kApplyRowSplit, part = blockIdx.x - band * kApplyRowSplit;
+    const int band = blockIdx.x / row_split, part = blockIdx.x - band * row_split;
     const int b0 = bands.start[band], b1 = bands.start[band + 1];
-    const int per = (b1 - b0 + kApplyRowSplit - 1) / kApplyRowSplit;
+    const int per = (b1 - b0 + row_split - 1) / row_split;
     const int y_begin = b0 + part * per, y_end = min(y_begin + per, b1);
     if (y_begin >= y_end) return;
     const int cy = band - 1;                                         // cell row: tile rows (cy, cy+1) clamped
@@ -504,8 +506,13 @@ void launch_clahe_apply_only(const uint8_t* src, int src_pitch, int64_t src_stri
     const int nchunks = (W + 255) / 256;
     int nwarps = nchunks < 32 ? nchunks : 32;
     if (nwarps < 8) nwarps = (8 / nchunks) * nchunks;          // row groups fill the CTA up to 8 warps
-    launch_pdl(clahe_apply_kernel, dim3((kClaheTiles + 1) * kApplyRowSplit, n_streams), dim3(32 * nwarps), 0, st,
-        src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, inv_tw, inv_th, bands, luts);
+    int row_split = n_streams >= 64 ? 1 : n_streams >= 8 ? 2 : 4;
+    {
+        static const char* e = getenv("VS_CLAHE_ROW_SPLIT");      // measurement knob
+        if (e && atoi(e) > 0) row_split = atoi(e);
+    }
+    launch_pdl(clahe_apply_kernel, dim3((kClaheTiles + 1) * row_split, n_streams), dim3(32 * nwarps), 0, st,
+        src, src_pitch, src_stride, dst, dst_pitch, dst_stride, W, H, inv_tw, inv_th, bands, luts, row_split);
 }
 
 void launch_clahe(const uint8_t* src, int src_pitch, int64_t src_stride, uint8_t* dst, int dst_pitch,

@@ -165,6 +165,11 @@ VS_API int vs_tracker_set_frontend_flags(struct vs_tracker* t, int32_t equalize,
 VS_API int vs_tracker_set_reject_callback(struct vs_tracker* t, vs_reject_fn fn, void* user);
 VS_API int vs_tracker_reset(struct vs_tracker* t, int32_t stream /* -1 = all */);
 /* number of CUDA kernels this handle has launched so far (bench.py "gpu_launches") */
+/* Debug aid: the newest frame's pyramid block of one stream exactly as the LK kernel sees it (padded levels).
+ * layout[4 l .. 4 l + 3] = byte offset of pixel (0, 0), pitch, width, height of level l (l < 6); layout[24] = block size
+ * in bytes, layout[25] / layout[26] = border columns / rows stored around every level.  out may be NULL (layout only). */
+VS_API int vs_tracker_debug_read_pyramid(struct vs_tracker* t, int32_t stream, uint8_t* out, int64_t cap_bytes,
+                                         int64_t* layout /* [27] */, int32_t* n_levels);
 VS_API int64_t vs_tracker_launch_count(const struct vs_tracker* t);
 /* Debug aid: a handle created with VS_DEBUG_GUARD=1 in the environment brackets every device buffer with 4 KiB guard
  * bands; this synchronises the device and returns how many guard bytes have been overwritten since creation

@@ -1070,6 +1070,35 @@ int64_t vs_tracker_debug_guard_check(vs_tracker* t) {
     return bad;
 }
 
+int vs_tracker_debug_read_pyramid(vs_tracker* t, int32_t stream, uint8_t* out, int64_t cap_bytes, int64_t* layout, int32_t* n_levels) {
+    if (!t || !layout || !n_levels) { set_error("vs_tracker_debug_read_pyramid: null argument"); return VS_ERR_INVALID; }
+    if (!t->lanes.empty()) {
+        int l = 0;
+        while (l + 1 < (int)t->lanes.size() && stream >= t->lane_s0[l + 1]) ++l;
+        stream -= t->lane_s0[l];
+        t = t->lanes[l];
+    }
+    if (stream < 0 || stream >= t->B) { set_error("vs_tracker_debug_read_pyramid: bad stream"); return VS_ERR_INVALID; }
+    VS_CUDA_TRY(cudaSetDevice(t->cfg.device));
+    const int nl = t->built[t->cur];
+    for (int l = 0; l < kMaxLevels; ++l) {
+        layout[4 * l + 0] = t->pd.lv[l].offset;
+        layout[4 * l + 1] = t->pd.lv[l].pitch;
+        layout[4 * l + 2] = t->pd.lv[l].w;
+        layout[4 * l + 3] = t->pd.lv[l].h;
+    }
+    layout[4 * kMaxLevels] = t->pd.stream_bytes;
+    layout[4 * kMaxLevels + 1] = kPyrPadX;
+    layout[4 * kMaxLevels + 2] = kPyrPadY;
+    *n_levels = nl;
+    if (out) {
+        if (cap_bytes < t->pd.stream_bytes) { set_error("vs_tracker_debug_read_pyramid: buffer below %lld bytes", (long long)t->pd.stream_bytes); return VS_ERR_CAPACITY; }
+        VS_CUDA_TRY(cudaStreamSynchronize(t->stream));
+        VS_CUDA_TRY(cudaMemcpy(out, t->d_pyr[t->cur] + (int64_t)stream * t->pd.stream_bytes, (size_t)t->pd.stream_bytes, cudaMemcpyDeviceToHost));
+    }
+    return VS_OK;
+}
+
 int64_t vs_tracker_launch_count(const vs_tracker* t) {
     if (!t) return 0;
     int64_t n = t->launches;

@@ -260,6 +260,22 @@ class BatchTracker:
         """Overwritten guard bytes around the handle's device buffers (needs VS_DEBUG_GUARD=1 at creation; -1 without)."""
         return int(self._lib.vs_tracker_debug_guard_check(self._h))
 
+    def debug_read_pyramid(self, stream: int = 0):
+        """[(level incl. its stored border, pad_x, pad_y)] of the newest frame of ``stream``, as the LK kernel sees it."""
+        layout = (C.c_int64 * 27)()
+        nl = C.c_int32(0)
+        _abi.check(self._lib.vs_tracker_debug_read_pyramid(self._h, stream, None, 0, layout, C.byref(nl)))
+        buf = np.zeros(layout[24], np.uint8)
+        _abi.check(self._lib.vs_tracker_debug_read_pyramid(self._h, stream, buf.ctypes.data, buf.size, layout, C.byref(nl)))
+        px, py = int(layout[25]), int(layout[26])
+        out = []
+        for l in range(nl.value):
+            off, pitch, w, h = (int(layout[4 * l + k]) for k in range(4))
+            start = off - py * pitch - px
+            block = buf[start:start + (h + 2 * py) * pitch].reshape(h + 2 * py, pitch)
+            out.append((block[:, :w + 2 * px].copy(), px, py))
+        return out
+
     @property
     def launch_count(self) -> int:
         return int(self._lib.vs_tracker_launch_count(self._h))

@@ -202,6 +202,25 @@ VS_API int vs_stage_ransac(struct vs_tracker* t, const float* a_xy, const float*
 VS_API int vs_stage_ransac_mark(struct vs_tracker* t, const double* f9, const float* a_xy, const float* b_xy,
                                 const float* next_px_xy, int32_t n, double edge_factor, const uint8_t* base_status,
                                 uint8_t* status);
+/* ---- allocation-free entry point ----
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * CLAHE(clipLimit 3.0, 8 x 8 tiles) of n_images 8-bit DEVICE images, the same two kernels as vs_stage_clahe and the frame
+ * path (bit-identical output, == cv::CLAHE::apply).  d_src / d_dst: device memory of the CURRENT device, image i at
+ * d_* + i * *_image_stride, rows *_pitch bytes apart; pointers, pitches and image strides multiples of 16, pitches >=
+ * width, 32 <= width, height <= 16384; d_src and d_dst must not overlap.  cuda_stream: a cudaStream_t (NULL = the
+ * default stream).  The call enqueues two kernels on that stream and returns without synchronising; it needs no
+ * tracker handle, calls no cudaMalloc / cudaFree / allocating library routine and creates no stream or event.
+ * Limit: n_images <= VS_CLAHE_NO_ALLOC_MAX_IMAGES, else VS_ERR_CAPACITY (split the batch into calls on ONE stream).
+ * Its scratch — the 64 tile look-up tables of each image, 16 KiB per image — is a static device array inside the
+ * library: every GPU that loads the library holds VS_CLAHE_NO_ALLOC_MAX_IMAGES x 16 KiB = 1 MiB until the process
+ * exits; ALL calls on a device share it, so calls that overlap on the GPU (different streams, concurrent launches of one
+ * captured graph) RACE on it — calls on one stream are ordered and safe; it keeps the previous call's contents, which is
+ * harmless: every table entry a call reads is written by that call first. */
+#define VS_CLAHE_NO_ALLOC_MAX_IMAGES 64
+VS_API int vs_clahe_no_alloc(const uint8_t* d_src, int32_t src_pitch, int64_t src_image_stride, uint8_t* d_dst,
+                             int32_t dst_pitch, int64_t dst_image_stride, int32_t width, int32_t height,
+                             int32_t n_images, void* cuda_stream);
 /* ---- measurement hooks (bench.py) ---- */
 /* The handle's CUDA stream (a cudaStream_t): lets a caller record its own events on the stream the
  * kernels are launched on, or order its own work after a track call. */

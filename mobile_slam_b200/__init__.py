@@ -7,8 +7,8 @@ all as hand-written CUDA kernels behind the C ABI in ``include/vs_tracker.h``.
 from ._abi import (VS_RANSAC_OFF, VS_RANSAC_DEVICE, VS_RANSAC_CALLBACK, VS_CAM_KANNALA_BRANDT, VS_CAM_MEI,
                    VS_CAM_PINHOLE, VS_CAM_SCARAMUZZA, VsError, load, LIB_PATH)
 from .feature_tracker import (BatchTracker, CameraParams, FeatureTracker, StreamResult, TrackerConfig,
-                              config_from_synth)
+                              clahe_no_alloc, config_from_synth)
 
-__all__ = ["BatchTracker", "CameraParams", "FeatureTracker", "StreamResult", "TrackerConfig", "config_from_synth",
+__all__ = ["BatchTracker", "CameraParams", "FeatureTracker", "StreamResult", "TrackerConfig", "config_from_synth", "clahe_no_alloc",
            "VsError", "load", "LIB_PATH", "VS_RANSAC_OFF", "VS_RANSAC_DEVICE", "VS_RANSAC_CALLBACK",
            "VS_CAM_KANNALA_BRANDT", "VS_CAM_MEI", "VS_CAM_PINHOLE", "VS_CAM_SCARAMUZZA"]

@@ -54,7 +54,7 @@ EXPORTS = [
     "vs_last_error", "vs_abi_version", "vs_tracker_create", "vs_tracker_destroy",
     "vs_tracker_default_config", "vs_tracker_track", "vs_tracker_track_batch",
     "vs_tracker_track_batch_device", "vs_tracker_submit_batch", "vs_tracker_wait", "vs_tracker_fetch_results", "vs_tracker_set_params",
-    "vs_tracker_set_reject_callback", "vs_tracker_reset", "vs_tracker_launch_count", "vs_tracker_debug_guard_check", "vs_tracker_debug_read_pyramid",
+    "vs_tracker_set_reject_callback", "vs_tracker_reset", "vs_tracker_launch_count", "vs_tracker_debug_guard_check", "vs_clahe_no_alloc", "vs_tracker_debug_read_pyramid",
     "vs_tracker_last_device_ms", "vs_stage_clahe", "vs_stage_pyramid", "vs_stage_lk",
     "vs_stage_min_eig", "vs_stage_good_features", "vs_stage_undistort", "vs_stage_set_mask",
     "vs_stage_ransac", "vs_tracker_cuda_stream", "vs_tracker_set_profiling", "vs_tracker_get_profile",
@@ -109,6 +109,7 @@ def load():
     lib.vs_tracker_debug_guard_check.argtypes = [vp]
     lib.vs_tracker_debug_guard_check.restype = i64
     lib.vs_tracker_debug_read_pyramid.argtypes = [vp, i32, vp, i64, C.POINTER(i64), C.POINTER(i32)]
+    lib.vs_clahe_no_alloc.argtypes = [vp, i32, i64, vp, i32, i64, i32, i32, i32, vp]
     lib.vs_tracker_launch_count.argtypes = [vp]
     lib.vs_tracker_launch_count.restype = i64
     lib.vs_tracker_last_device_ms.argtypes = [vp]

@@ -385,6 +385,18 @@ class BatchTracker:
         return {self._lib.vs_profile_kernel_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n.value)}
 
 
+CLAHE_NO_ALLOC_MAX_IMAGES = 64      # VS_CLAHE_NO_ALLOC_MAX_IMAGES (include/vs_tracker.h)
+
+
+def clahe_no_alloc(d_src: int, src_pitch: int, src_image_stride: int, d_dst: int, dst_pitch: int, dst_image_stride: int,
+                   width: int, height: int, n_images: int = 1, cuda_stream: int = 0) -> None:
+    """``vs_clahe_no_alloc``: CLAHE of ``n_images`` device images (raw device addresses) enqueued on ``cuda_stream`` without
+    any allocation — no handle needed; the scratch is a static device array shared by every call on the device (calls
+    that overlap on the GPU race; at most CLAHE_NO_ALLOC_MAX_IMAGES images per call).  Not synchronised."""
+    _abi.check(_abi.load().vs_clahe_no_alloc(d_src, src_pitch, src_image_stride, d_dst, dst_pitch, dst_image_stride,
+                                             width, height, n_images, cuda_stream or None))
+
+
 class FeatureTracker:
     """Drop-in mirror of ``frontend::FeatureTracker`` for one camera stream.
 

@@ -52,6 +52,7 @@ struct StParams {
     int64_t img_stride;       // bytes between two streams' images
     int W, H;
     int nx, ny, words_per_strip, rows_per_strip;   // strip grid (filled by launch_shi_tomasi)
+    int skip_masked_rows;     // walk only the row steps that can reach an unmasked pixel (filled by launch_shi_tomasi)
     const int* want;          // [n_streams] corners wanted; streams with want <= 0 are skipped (may be null)
     // analytic mask = base minus the min_dist discs of the kept features
     const int* kn;            // [n_streams] kept features (may be null = none)

@@ -268,6 +268,52 @@ VS_API int vs_ingest_submit_raw(struct vs_ingest* g, const uint8_t* const* frame
 VS_API int vs_ingest_wait(struct vs_ingest* g, vs_track_result* out /* [n_streams] */);
 VS_API void vs_ingest_destroy(struct vs_ingest* g);
 
+/* ---- device feature bank: frontend::FeatureManager for n_streams independent streams -----------------
+ * Replaces, per stream, the class of /root/reference/include/frontend/feature_manager.h:70-92 whose methods live in
+ * /root/reference/src/frontend/feature_manager.cpp (cited per entry point).  Feature records are rows of 7 doubles
+ * [x, y, z, u, v, vx, vy] (common/image_frame.h:14, the layout vs_pack_image_features writes).  WINDOW_SIZE is 10
+ * (utility/config.h:11): a feature holds at most VS_BANK_MAX_OBS observations.  Decisions, parallax sums and shifted
+ * depths are bit-equal to the reference; triangulated depths agree to rounding (the SVD is a Jacobi iteration here,
+ * Eigen::JacobiSVD there).  All calls synchronise the bank's own stream before returning. */
+#define VS_BANK_WINDOW_SIZE 10
+#define VS_BANK_MAX_OBS (VS_BANK_WINDOW_SIZE + 1)
+struct vs_bank;
+VS_API int vs_bank_create(int32_t device, int32_t n_streams, int32_t capacity /* features per stream */, struct vs_bank** out);
+VS_API void vs_bank_destroy(struct vs_bank* b);
+/* clearState, feature_manager.cpp:11-13; stream -1 = all */
+VS_API int vs_bank_clear(struct vs_bank* b, int32_t stream);
+/* addFeatureAndCheckParallax, feature_manager.cpp:27-73 (+ compensatedParallax2 :264-294), every stream in one launch.
+ * frame_count[s], n[s] records ids[s][max_n] / rec[s][max_n][7] (unique ids, any order: the std::map order of
+ * common::ImageData is applied).  is_key[s] = the method's return value; optional outputs: last_track_num_, and the
+ * parallax sum / count the decision was taken on.  VS_ERR_CAPACITY when a stream's bank is full. */
+VS_API int vs_bank_add_frame(struct vs_bank* b, const int32_t* frame_count, const int32_t* n, const int32_t* ids,
+                             const double* rec, int32_t max_n, double min_parallax, double focal_length, int32_t* is_key,
+                             int32_t* last_track_num, double* parallax_sum, int32_t* parallax_num);
+/* The same, fed from the DEVICE-resident results of the tracker handle's last frame: the publish loop (track_cnt > 1,
+ * measurement_processor.cpp:210-231, vio_engine.cpp:219-239) runs on the device and only the decisions cross PCIe.
+ * The bank must have the handle's stream count and device. */
+VS_API int vs_bank_add_frame_from_tracker(struct vs_bank* b, struct vs_tracker* t, const int32_t* frame_count,
+                                          double min_parallax, double focal_length, int32_t* is_key, int32_t* last_track_num);
+/* Window maintenance, op[s]: 0 nothing, 1 removeBack (feature_manager.cpp:237-249), 2 removeFront(frame_count[s])
+ * (:251-266), 3 removeBackShiftDepth (:208-235; rp[s] = marg_R (9, row-major) marg_P (3) new_R (9) new_P (3)),
+ * 4 removeFailures (:112-118).  init_depth = g_config.estimator.init_depth. */
+VS_API int vs_bank_slide(struct vs_bank* b, const int32_t* op, const int32_t* frame_count_or_null,
+                         const double* rp_or_null /* [n_streams][24] */, double init_depth);
+/* triangulateAcrossAllViews, feature_manager.cpp:142-194: poses[s][VS_BANK_MAX_OBS][12] = sliding_window[i].R (row-major) | .P;
+ * active_or_null[s] == 0 leaves stream s alone (its estimator has no full window yet) */
+VS_API int vs_bank_triangulate(struct vs_bank* b, const double* poses, const double* t_ic /* [3] */,
+                               const double* r_ic /* [9] row-major */, double init_depth, const int32_t* active_or_null);
+/* getDepthVector (:130-140) of one stream, *n = getFeatureCount (:15-25); out may be null to ask for the count */
+VS_API int vs_bank_get_depth_vector(struct vs_bank* b, int32_t stream, int32_t max_n, double* out, int32_t* n);
+/* setDepth (:94-110, clear = 0) / clearDepth (:120-128, clear = 1) */
+VS_API int vs_bank_set_depth(struct vs_bank* b, int32_t stream, const double* x, int32_t n, int32_t clear);
+/* getCorresponding (:75-92): pairs[k] = ray in frame_l (3) | ray in frame_r (3), list order; pairs may be null */
+VS_API int vs_bank_get_corresponding(struct vs_bank* b, int32_t stream, int32_t frame_l, int32_t frame_r, int32_t max_n,
+                                     double* pairs, int32_t* n);
+/* feature_bank_ of one stream in list order (any output may be null); obs[max_n][VS_BANK_MAX_OBS][7] */
+VS_API int vs_bank_export(struct vs_bank* b, int32_t stream, int32_t max_n, int32_t* ids, int32_t* start_frame,
+                          int32_t* n_obs, double* depth, int32_t* solve_flag, double* obs, int32_t* n);
+
 /* total_ms[i] / launches[i] for kernel slot i < *n_out <= max_n; names from vs_profile_kernel_name */
 VS_API int vs_tracker_get_profile(const struct vs_tracker* t, int32_t max_n, float* total_ms, int32_t* launches,
                                   int32_t* n_out);

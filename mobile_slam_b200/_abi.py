@@ -61,6 +61,9 @@ EXPORTS = [
     "vs_profile_kernel_name", "vs_pack_image_features", "vs_tracker_set_frontend_flags",
     "vs_tracker_get_config", "vs_image_decode_gray", "vs_image_read_gray", "vs_ingest_create", "vs_ingest_submit_files",
     "vs_ingest_submit_raw", "vs_ingest_wait", "vs_ingest_destroy", "vs_stage_ransac_mark",
+    "vs_bank_create", "vs_bank_destroy", "vs_bank_clear", "vs_bank_add_frame", "vs_bank_add_frame_from_tracker",
+    "vs_bank_slide", "vs_bank_triangulate", "vs_bank_get_depth_vector", "vs_bank_set_depth",
+    "vs_bank_get_corresponding", "vs_bank_export",
 ]
 
 _lib = None
@@ -132,6 +135,19 @@ def load():
     lib.vs_pack_image_features.restype = C.c_int
     lib.vs_profile_kernel_name.argtypes = [i32]
     lib.vs_profile_kernel_name.restype = C.c_char_p
+    pi32, pf64 = C.POINTER(i32), C.POINTER(f64)
+    lib.vs_bank_create.argtypes = [i32, i32, i32, C.POINTER(vp)]
+    lib.vs_bank_destroy.argtypes = [vp]
+    lib.vs_bank_destroy.restype = None
+    lib.vs_bank_clear.argtypes = [vp, i32]
+    lib.vs_bank_add_frame.argtypes = [vp, pi32, pi32, pi32, pf64, i32, f64, f64, pi32, pi32, pf64, pi32]
+    lib.vs_bank_add_frame_from_tracker.argtypes = [vp, vp, pi32, f64, f64, pi32, pi32]
+    lib.vs_bank_slide.argtypes = [vp, pi32, pi32, pf64, f64]
+    lib.vs_bank_triangulate.argtypes = [vp, pf64, pf64, pf64, f64, pi32]
+    lib.vs_bank_get_depth_vector.argtypes = [vp, i32, i32, pf64, pi32]
+    lib.vs_bank_set_depth.argtypes = [vp, i32, pf64, i32, i32]
+    lib.vs_bank_get_corresponding.argtypes = [vp, i32, i32, i32, i32, pf64, pi32]
+    lib.vs_bank_export.argtypes = [vp, i32, i32, pi32, pi32, pi32, pf64, pi32, pf64, pi32]
     _lib = lib
     return lib
 

@@ -781,6 +781,7 @@ static int enqueue_frame(vs_tracker* t, const uint8_t* d_frames, int32_t stride,
     }
     prof_tick(t, PK_INPUT);
     if (direct_results(t)) point_results(t, t->h_block + (size_t)slot * t->h_block_bytes);
+    t->last_results = direct_results(t) ? t->h_block + (size_t)slot * t->h_block_bytes : t->d_rblock;
     const int rc = run_frame(t, img, pitch, istride);
     if (direct_results(t)) point_results(t, t->d_rblock);      // stage entry points and fetches use the device block
     if (rc != VS_OK) return rc;

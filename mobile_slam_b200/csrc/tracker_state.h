@@ -104,6 +104,7 @@ struct vs_tracker {
     uint8_t* h_block = nullptr;   // results: hdr | ids | cnt | pts | un | vel
     size_t h_block_bytes = 0;
     uint8_t* d_rblock = nullptr;
+    const uint8_t* last_results = nullptr;   // block the last frame's kernels wrote (device block, or the pinned slot of a small handle)
     // timestamps are read in place from pinned host memory by select_finish: a ring of slots, each guarded by an event
     // recorded after the frame that reads it, so back-to-back unsynchronised calls never overwrite a slot still in use
     static constexpr int kTimeRing = 8;

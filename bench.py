@@ -535,6 +535,41 @@ def measure(args, name, rank, world, local_rank, D, clocks, compact=False):
         step += 1
     prof = bt.profile()
     bt.set_profiling(False)
+
+    # ---- (2b) the downstream consumers: the device feature bank fed from the tracker's device-resident
+    #          results (addFeatureAndCheckParallax + the window slide the decision asks for), timed per call on the host
+    #          with the tracker's frame already finished — wall clock of the C-ABI calls, which synchronise ----
+    consumers = None
+    if not compact:
+        from mobile_slam_b200.feature_bank import (OP_NONE, OP_REMOVE_BACK, OP_REMOVE_FRONT, WINDOW_SIZE as BANK_WIN,
+                                                   FeatureBank)
+        bank = FeatureBank(S, capacity=1024, device=local_rank, focal_length=float(cfg.get("focal_length", 460.0)))
+        fcs = np.zeros(S, np.int32)
+        add_s, slide_s, n_t, keys_sum, in_bank = 0.0, 0.0, 0, 0.0, 0
+        for i in range(BANK_WIN + 2 + K):
+            bt.track_device(d_frames[bounce(step, n_buf)].data_ptr(), W, H * W, times(step), to_host=False)
+            step += 1
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            keys = bank.add_frames_from_tracker(bt, fcs)
+            t1 = time.perf_counter()
+            full = fcs >= BANK_WIN
+            ops = np.where(full, np.where(keys, OP_REMOVE_BACK, OP_REMOVE_FRONT), OP_NONE).astype(np.int32)
+            fcs = np.where(full, fcs, fcs + 1).astype(np.int32)
+            t2 = time.perf_counter()
+            bank.slide(ops, fcs)
+            t3 = time.perf_counter()
+            if i >= BANK_WIN + 2:
+                add_s += t1 - t0
+                slide_s += t3 - t2
+                keys_sum += float(np.mean(keys))
+                n_t += 1
+        in_bank = float(np.mean([len(bank.export(s_)[0]) for s_ in range(0, S, max(1, S // 8))]))
+        bank.close()
+        consumers = {"what": "vs_bank_add_frame_from_tracker + vs_bank_slide per step, all streams of this GPU (rank 0)",
+                     "add_frame_ms": 1e3 * add_s / n_t, "slide_ms": 1e3 * slide_s / n_t,
+                     "key_frame_frac": keys_sum / n_t, "features_in_bank_mean": in_bank,
+                     "streams": S, "timing": "host wall clock of the synchronous C-ABI calls"}
     bt.close()
 
     # ---- (3) end to end through the C ABI with host frames: the handle is split into pipeline lanes so the H2D copy
@@ -638,7 +673,7 @@ def measure(args, name, rank, world, local_rank, D, clocks, compact=False):
     total_frames = D.sum(float(S * K))
     S_max = int(D.max(float(S)))
     out = dict(name=name, cfg=cfg, S=S, S_max=S_max, total_frames=total_frames, dev_ms=dev_ms, rep_ms=rep_ms,
-               launches=int(launches), prof=prof, e2e_s=e2e_s, e2e_sync_s=e2e_sync_s, d2h_bytes=d2h_bytes,
+               launches=int(launches), prof=prof, consumers=consumers, e2e_s=e2e_s, e2e_sync_s=e2e_sync_s, d2h_bytes=d2h_bytes,
                step_bytes=step_bytes, gather_ms=gather_ms, h2d_solo=h2d_solo, h2d_all_sum=h2d_all_sum,
                h2d_all_min=h2d_all_min, lat=lat, n_feat_mean=n_feat_mean, pub_mean=pub_mean, n_buf=n_buf,
                value=total_frames / (dev_ms * 1e-3), e2e_value=total_frames / e2e_s, h_frames=h_frames)
@@ -799,6 +834,8 @@ def run_ours(args, rank, world, local_rank):
         "cpu_baseline": cpu,
         "clocks": clocks.summary(),
     }
+    if m.get("consumers"):
+        line["consumers"] = m["consumers"]
     if m1 is not None:
         R1 = roofline_of(m1, K, world, peak, peak_src)
         line["c1"] = {"config": workload_config(args, m1["cfg"], m1["S"], name="C1"), "value": m1["value"],

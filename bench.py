@@ -543,7 +543,9 @@ def measure(args, name, rank, world, local_rank, D, clocks, compact=False):
     if not compact:
         from mobile_slam_b200.feature_bank import (OP_NONE, OP_REMOVE_BACK, OP_REMOVE_FRONT, WINDOW_SIZE as BANK_WIN,
                                                    FeatureBank)
-        bank = FeatureBank(S, capacity=1024, device=local_rank, focal_length=float(cfg.get("focal_length", 460.0)))
+        # a bank holds every feature seen inside the window (WINDOW_SIZE + 1 frames): three times max_cnt is ample here
+        bank = FeatureBank(S, capacity=min(8192, max(1024, 3 * int(cfg["max_cnt"]))), device=local_rank,
+                           focal_length=float(cfg.get("focal_length", 460.0)))
         fcs = np.zeros(S, np.int32)
         add_s, slide_s, n_t, keys_sum, in_bank = 0.0, 0.0, 0, 0.0, 0
         for i in range(BANK_WIN + 2 + K):

@@ -1,5 +1,7 @@
 // Host-callable launchers of the vs_tracker CUDA kernels (one .cu per stage).
 #pragma once
+#include <cuda.h>   // CUtensorMap (type only; the encode function is fetched through the runtime)
+
 #include "vs_common.cuh"
 
 namespace vs {
@@ -42,7 +44,17 @@ struct LkParams {
     uint8_t* status;          // [n_streams][cap] raw LK status
     int* work_counters;       // [2] persistent-warp work queue heads (zeroed at create), alternated by work_seq
     int work_seq;             // launch sequence number of this handle
+    // TMA staging (VS_LK_TMA=1, A/B only): tensor maps of both pyramid buffers and which of them is prev / next
+    const struct LkTmaMaps* tma_maps;   // host pointer, may be null
+    int prev_buf, next_buf;
 };
+// One 3-D tensor map (x bytes, rows, stream) per pyramid buffer, level and tile height (24 template rows / 32 search rows)
+// over the level's PADDED block, so tile origins are never negative.
+struct LkTmaMaps {
+    CUtensorMap m[2][kMaxLevels][2];
+};
+// fills the maps of one handle (driver entry point cuTensorMapEncodeTiled through the runtime); 0 on success
+int lk_build_tma_maps(LkTmaMaps* out, uint8_t* const d_pyr[2], const PyrDesc& pd, int n_streams);
 int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches);
 
 // ---- shitomasi.cu (K5, K6) ----

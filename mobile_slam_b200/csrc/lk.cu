@@ -7,6 +7,10 @@
 // The Scharr derivative images OpenCV precomputes are derived here from the staged u8 tile:
 // derivative = 0 where the derivative sample lies outside the level (BORDER_CONSTANT), while image
 // samples outside the level are REFLECT_101 — exactly the padding buildOpticalFlowPyramid applies.
+#include <cstdlib>
+#include <map>
+#include <mutex>
+
 #include "kernels.h"
 
 namespace vs {
@@ -283,6 +287,34 @@ __device__ __forceinline__ void stage_rows16(uint32_t* tile, const uint8_t* __re
     asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
+// The same tile by ONE bulk tensor copy (TMA): lane 0 arms the warp's mbarrier with the byte count and issues
+// cp.async.bulk.tensor.3d (x = byte column, y = row, z = stream) on the tensor map of the level's padded block; every lane
+// then waits for the barrier's phase.  ROWS selects the map (24 template rows / 32 search rows).  A/B variant of
+// stage_rows16 (VS_LK_TMA=1): same bytes in the same layout, one instruction instead of three per lane.
+struct TmaWarp {
+    uint32_t bar;       // shared address of this warp's mbarrier
+    uint32_t phase;
+};
+template <int ROWS>
+__device__ __forceinline__ void stage_rows_tma(uint32_t* tile, const CUtensorMap* map, int x0, int y0, int stream, int lane,
+                                               TmaWarp& tw) {
+    const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(tile);
+    if (lane == 0) {
+        // the tile was last touched through the generic proxy (ld.shared of the previous iteration): order those before
+        // the async-proxy write
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tw.bar), "r"(ROWS * kFastPitch) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                     ::"r"(tile_s), "l"(map), "r"(x0 + kPyrPadX), "r"(y0 + kPyrPadY), "r"(stream), "r"(tw.bar) : "memory");
+    }
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(tw.bar), "r"(tw.phase) : "memory");
+    }
+    tw.phase ^= 1u;
+}
+
 // 12 bytes of a tile row starting at byte `sb`, re-aligned so that a0 holds bytes sb..sb+3, a1 sb+4..sb+7, a2 sb+8..sb+11
 __device__ __forceinline__ void load_aligned3(const uint32_t* trow, int sb, uint32_t& a0, uint32_t& a1, uint32_t& a2) {
     const uint32_t* q = trow + (sb >> 2);
@@ -294,7 +326,9 @@ __device__ __forceinline__ void load_aligned3(const uint32_t* trow, int sb, uint
 }
 
 // one feature (stream s, slot i) on one warp
-__device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int i, uint32_t* tile, int lane) {
+template <bool TMA>
+__device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int i, uint32_t* tile, int lane,
+                                                  const LkTmaMaps* maps, TmaWarp& tw) {
     constexpr int WIN = 21, NSEG = 3, NRUN = WIN * NSEG;
     const float hw = (float)(WIN - 1) * 0.5f;
 
@@ -341,7 +375,8 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
         // ---- template: tile origin (x aligned down to 16, ipy - 1), 24 rows x 48 bytes ----
         const int tx0 = (ipx - 1) & ~15, ax = (ipx - 1) - tx0;
         __syncwarp();
-        if (level >= kPyrFirstPaddedLevel) stage_rows16<WIN + 3, true>(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, lane);
+        if constexpr (TMA) stage_rows_tma<WIN + 3>(tile, &maps->m[p.prev_buf][level][0], tx0, ipy - 1, s, lane, tw);
+        else if (level >= kPyrFirstPaddedLevel) stage_rows16<WIN + 3, true>(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, lane);
         else stage_rows16<WIN + 3, false>(tile, prev_base + L.offset, L.w, L.h, L.pitch, tx0, ipy - 1, lane);
         __syncwarp();
         const bool border = ipx < 0 || ipy < 0 || ipx + WIN + 1 > L.w || ipy + WIN + 1 > L.h;
@@ -435,7 +470,8 @@ __device__ __forceinline__ void lk_fast21_feature(const LkParams& p, int s, int 
                 tox = (iqx - kLkMargin) & ~15;
                 toy = iqy - kLkMargin;
                 __syncwarp();
-                if (level >= kPyrFirstPaddedLevel) stage_rows16<kFastRows, true>(tile, J, L.w, L.h, L.pitch, tox, toy, lane);
+                if constexpr (TMA) stage_rows_tma<kFastRows>(tile, &maps->m[p.next_buf][level][1], tox, toy, s, lane, tw);
+                else if (level >= kPyrFirstPaddedLevel) stage_rows16<kFastRows, true>(tile, J, L.w, L.h, L.pitch, tox, toy, lane);
                 else stage_rows16<kFastRows, false>(tile, J, L.w, L.h, L.pitch, tox, toy, lane);
                 __syncwarp();
                 staged = true;
@@ -513,9 +549,66 @@ __global__ void __launch_bounds__(32 * kLkWarpsPerCta, 5) lk_fast21_kernel(LkPar
         w = __shfl_sync(0xffffffffu, w, 0);
         if (w >= total) break;
         const int s = w / max_features, i = w - s * max_features;
-        if (i < __ldg(p.counts + s)) lk_fast21_feature(p, s, i, tile, lane);
+        TmaWarp none{0u, 0u};
+        if (i < __ldg(p.counts + s)) lk_fast21_feature<false>(p, s, i, tile, lane, nullptr, none);
         __syncwarp();
     }
+}
+
+// The same kernel with the tiles staged by TMA (VS_LK_TMA=1): the tensor maps travel as a __grid_constant__ parameter
+// (3 KB), each warp owns one mbarrier.
+__global__ void __launch_bounds__(32 * kLkWarpsPerCta, 5) lk_fast21_tma_kernel(LkParams p, int n_streams, int max_features,
+                                                                            int* counters, int which,
+                                                                            const __grid_constant__ LkTmaMaps maps) {
+    pdl_entry();
+    __shared__ __align__(128) uint32_t s_tiles[kLkWarpsPerCta][kFastWarpSmem / 4];
+    __shared__ __align__(8) unsigned long long s_bar[kLkWarpsPerCta];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (blockIdx.x == 0 && threadIdx.x == 0) counters[which ^ 1] = 0;
+    uint32_t* tile = s_tiles[warp];
+    TmaWarp tw{(uint32_t)__cvta_generic_to_shared(&s_bar[warp]), 0u};
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tw.bar) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    const int total = n_streams * max_features;
+    int* ctr = counters + which;
+    for (;;) {
+        int w = 0;
+        if (lane == 0) w = atomicAdd(ctr, 1);
+        w = __shfl_sync(0xffffffffu, w, 0);
+        if (w >= total) break;
+        const int s = w / max_features, i = w - s * max_features;
+        if (i < __ldg(p.counts + s)) lk_fast21_feature<true>(p, s, i, tile, lane, &maps, tw);
+        __syncwarp();
+    }
+}
+
+int lk_build_tma_maps(LkTmaMaps* out, uint8_t* const d_pyr[2], const PyrDesc& pd, int n_streams) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) return -1;
+    EncodeFn encode = reinterpret_cast<EncodeFn>(fn);
+    static_assert(kPyrFirstPaddedLevel == 0, "the TMA variant addresses every level through its padded block");
+    for (int b = 0; b < 2; ++b)
+        for (int l = 0; l < kMaxLevels; ++l)
+            for (int k = 0; k < 2; ++k) {
+                const LevelDesc& L = pd.lv[l];
+                void* base = d_pyr[b] + (L.offset - (int64_t)kPyrPadY * L.pitch - kPyrPadX);
+                const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.h + 2 * kPyrPadY), (cuuint64_t)n_streams};
+                const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)pd.stream_bytes};
+                const cuuint32_t box[3] = {(cuuint32_t)kFastPitch, (cuuint32_t)(k == 0 ? 21 + 3 : kFastRows), 1u};
+                const cuuint32_t estr[3] = {1u, 1u, 1u};
+                if (encode(&out->m[b][l][k], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+                    return -2;
+            }
+    return 0;
 }
 
 int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t st, int64_t* launches) {
@@ -541,7 +634,13 @@ int launch_lk(const LkParams& p, int n_streams, int max_features, cudaStream_t s
             resident = r;
         }
         const int need = (n_streams * max_features + kLkWarpsPerCta - 1) / kLkWarpsPerCta;
-        launch_pdl(lk_fast21_kernel, dim3(need < resident ? need : resident), dim3(32 * kLkWarpsPerCta), 0, st, p, n_streams, max_features,
+        // VS_LK_TMA=1: tiles staged by cp.async.bulk.tensor instead of cp.async (A/B)
+        static const bool want_tma = [] { const char* e = getenv("VS_LK_TMA"); return e && atoi(e) != 0; }();
+        if (want_tma && p.tma_maps)
+            launch_pdl(lk_fast21_tma_kernel, dim3(need < resident ? need : resident), dim3(32 * kLkWarpsPerCta), 0, st, p, n_streams,
+                       max_features, p.work_counters, p.work_seq & 1, *p.tma_maps);
+        else
+            launch_pdl(lk_fast21_kernel, dim3(need < resident ? need : resident), dim3(32 * kLkWarpsPerCta), 0, st, p, n_streams, max_features,
                                                                                           p.work_counters, p.work_seq & 1);
     } else {
         const int smem = kLkWarpsPerCta * lk_warp_smem(p.win);

@@ -414,6 +414,13 @@ int vs_tracker_create(const vs_tracker_config* cfg, vs_tracker_config* effective
     VS_TRY_CREATE(A.alloc(&t->d_fish_hw, (size_t)(t->W > t->H ? t->W : t->H) + 2));
     VS_TRY_CREATE(A.alloc(&t->d_cur_time, (size_t)B));
     VS_TRY_CREATE(A.alloc(&t->d_lk_counters, (size_t)2));
+    {   // A/B variant of the LK tile staging (VS_LK_TMA=1): tensor maps over the two pyramid buffers
+        const char* e = getenv("VS_LK_TMA");
+        if (e && atoi(e) != 0) {
+            t->lk_tma = new LkTmaMaps();
+            if (lk_build_tma_maps(t->lk_tma, t->d_pyr, t->pd, t->B) != 0) { delete t->lk_tma; t->lk_tma = nullptr; }
+        }
+    }
     g.cur_time = t->d_cur_time;
     VS_TRY_CREATE(A.alloc(&g.n, B));
     VS_TRY_CREATE(A.alloc(&g.pts, B * C));
@@ -505,6 +512,7 @@ void vs_tracker_destroy(vs_tracker* t) {
     if (t->stream) cudaStreamSynchronize(t->stream);
     t->arena.release();
     if (t->d_eig) cudaFree(t->d_eig);
+    delete t->lk_tma;
     if (t->h_block) cudaFreeHost(t->h_block);
     if (t->h_time) cudaFreeHost(t->h_time);
     if (t->h_wn) cudaFreeHost(t->h_wn);
@@ -555,6 +563,9 @@ static void fill_lk_params(vs_tracker* t, LkParams& p, int prev_buf, int next_bu
     p.status = status;
     p.work_counters = t->d_lk_counters;
     p.work_seq = t->lk_seq++;
+    p.tma_maps = t->lk_tma;
+    p.prev_buf = prev_buf;
+    p.next_buf = next_buf;
 }
 
 // build the pyramid of the new frame into buffer `buf` from a device image

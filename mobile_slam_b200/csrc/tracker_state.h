@@ -97,6 +97,7 @@ struct vs_tracker {
     int base_mode = 0, fcx = 0, fcy = 0, fr = 0;   // StParams::base_mode and the circle
     double* d_cur_time = nullptr;
     int* d_lk_counters = nullptr; // persistent-warp LK work queue heads
+    vs::LkTmaMaps* lk_tma = nullptr;   // tensor maps of d_pyr[0..1] (VS_LK_TMA=1 only), host memory
     int lk_seq = 0;
     float* d_eig = nullptr;       // lazily allocated dense eig map (stage API only)
     vs::GlueParams g{};

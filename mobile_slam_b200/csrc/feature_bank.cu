@@ -63,6 +63,7 @@ struct BankFrame {
     const float2* r_vel;
     int t_cap;
     int s0;                    // bank stream of the source's stream 0
+    int rec_cap;               // records a stream can bring (max_n / the tracker's capacity): size of the match array
     double parallax_threshold; // min_parallax / focal_length
     int* o_key;                // [B]
     int* o_track;              // [B]
@@ -94,12 +95,25 @@ __global__ void __launch_bounds__(kBankThreads) bank_add_kernel(BankDev b, BankF
     const int64_t so = (int64_t)s * b.cap;
     int* s_bid = smem;                         // [cap] ids in list order
     int* s_match = smem + b.cap;               // [max records] list position, -1 new, -2 not a record
+    int* s_hash = s_match + f.rec_cap;         // [pow2 >= 2 * cap] open-addressing table: list position or -1
     __shared__ int s_tracked, s_new, s_new_ok;
     const int n_rec = f.from_tracker ? min(f.r_hdr[(int64_t)ss * kHdrInts + H_N], f.t_cap) : min(f.n[ss], f.max_n);
     const int cnt = b.count[s];
     const int fc = f.frame_count[ss];
     if (tid == 0) { s_tracked = 0; s_new = 0; s_new_ok = 0; }
     for (int i = tid; i < cnt; i += kBankThreads) s_bid[i] = b.id[so + b.order[so + i]];
+    // the reference's find_if is a linear search (ids are unique in the list, so "first match" is "the match"): a hash
+    // table over the list, sized to at most half full, gives the same answer in O(1) per record
+    int hbits = 6;
+    while ((1 << hbits) < 2 * cnt) ++hbits;
+    const unsigned hmask = (1u << hbits) - 1u;
+    for (int i = tid; i <= (int)hmask; i += kBankThreads) s_hash[i] = -1;
+    __syncthreads();
+    auto hash_of = [&](int id) { return ((unsigned)id * 2654435761u) >> (32 - hbits); };
+    for (int i = tid; i < cnt; i += kBankThreads) {
+        unsigned h = hash_of(s_bid[i]);
+        while (atomicCAS(&s_hash[h], -1, i) != -1) h = (h + 1) & hmask;
+    }
     __syncthreads();
     auto rec_valid = [&](int r) { return f.from_tracker ? f.r_cnt[(int64_t)ss * f.t_cap + r] > 1 : true; };
     auto rec_id = [&](int r) { return f.from_tracker ? f.r_ids[(int64_t)ss * f.t_cap + r] : f.ids[(int64_t)ss * f.max_n + r]; };
@@ -121,8 +135,11 @@ __global__ void __launch_bounds__(kBankThreads) bank_add_kernel(BankDev b, BankF
         if (rec_valid(r)) {
             const int rid = rec_id(r);
             m = -1;
-            for (int i = 0; i < cnt; ++i)
-                if (s_bid[i] == rid) { m = i; break; }
+            for (unsigned h = hash_of(rid);; h = (h + 1) & hmask) {
+                const int pos = s_hash[h];
+                if (pos < 0) break;
+                if (s_bid[pos] == rid) { m = pos; break; }
+            }
             atomicAdd(m >= 0 ? &s_tracked : &s_new, 1);
         }
         s_match[r] = m;
@@ -443,7 +460,11 @@ using vs::set_error;
     if (!(bk)) { set_error("null bank handle"); return VS_ERR_INVALID; } \
     VS_CUDA_TRY(cudaSetDevice((bk)->device));
 
-static int bank_add_smem(const vs_bank* b, int rec_cap) { return (b->d.cap + rec_cap) * (int)sizeof(int); }
+static int bank_add_smem(const vs_bank* b, int rec_cap) {
+    int hsize = 64;
+    while (hsize < 2 * b->d.cap) hsize <<= 1;
+    return (b->d.cap + rec_cap + hsize) * (int)sizeof(int);
+}
 
 extern "C" {
 
@@ -570,6 +591,7 @@ int vs_bank_add_frame(vs_bank* b, const int32_t* frame_count, const int32_t* n, 
     f.max_n = max_n;
     f.from_tracker = 0;
     f.s0 = 0;
+    f.rec_cap = mn;
     f.parallax_threshold = min_parallax / focal_length;
     f.o_key = b->d_iparams + 2 * B;
     f.o_track = b->d_iparams + 3 * B;
@@ -613,12 +635,14 @@ int vs_bank_add_frame_from_tracker(vs_bank* b, vs_tracker* t, const int32_t* fra
         f.r_vel = reinterpret_cast<const float2*>(p);
         f.t_cap = (int)qC;
         f.s0 = first[l];
+        f.rec_cap = (int)qC;
         f.parallax_threshold = min_parallax / focal_length;
         f.o_key = b->d_iparams + 2 * B;
         f.o_track = b->d_iparams + 3 * B;
         f.o_psum = b->d_psum;
         f.o_pnum = b->d_pnum;
         const int smem = bank_add_smem(b, (int)qC);
+        if (smem > 200 * 1024) { set_error("bank: capacity %d + tracker capacity %d exceed the shared memory of one CTA", b->d.cap, (int)qC); return VS_ERR_CAPACITY; }
         VS_CUDA_TRY(vs::ensure_dyn_smem(reinterpret_cast<const void*>(vs::bank_add_kernel), smem));
         vs::bank_add_kernel<<<(unsigned)qB, vs::kBankThreads, smem, b->stream>>>(b->d, f, (int)qB);
     }

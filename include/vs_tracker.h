@@ -310,6 +310,10 @@ VS_API int vs_bank_set_depth(struct vs_bank* b, int32_t stream, const double* x,
 /* getCorresponding (:75-92): pairs[k] = ray in frame_l (3) | ray in frame_r (3), list order; pairs may be null */
 VS_API int vs_bank_get_corresponding(struct vs_bank* b, int32_t stream, int32_t frame_l, int32_t frame_r, int32_t max_n,
                                      double* pairs, int32_t* n);
+/* Debug aid like vs_tracker_debug_guard_check: with VS_DEBUG_GUARD=1 in the environment at vs_bank_create every device
+ * block of the bank lies between two guard bands; returns the number of guard bytes that changed (0 = no kernel stored
+ * outside its buffers), -1 when the bank was created without guards. */
+VS_API int64_t vs_bank_debug_guard_check(struct vs_bank* b);
 /* feature_bank_ of one stream in list order (any output may be null); obs[max_n][VS_BANK_MAX_OBS][7] */
 VS_API int vs_bank_export(struct vs_bank* b, int32_t stream, int32_t max_n, int32_t* ids, int32_t* start_frame,
                           int32_t* n_obs, double* depth, int32_t* solve_flag, double* obs, int32_t* n);

@@ -63,7 +63,7 @@ EXPORTS = [
     "vs_ingest_submit_raw", "vs_ingest_wait", "vs_ingest_destroy", "vs_stage_ransac_mark",
     "vs_bank_create", "vs_bank_destroy", "vs_bank_clear", "vs_bank_add_frame", "vs_bank_add_frame_from_tracker",
     "vs_bank_slide", "vs_bank_triangulate", "vs_bank_get_depth_vector", "vs_bank_set_depth",
-    "vs_bank_get_corresponding", "vs_bank_export",
+    "vs_bank_get_corresponding", "vs_bank_export", "vs_bank_debug_guard_check",
 ]
 
 _lib = None
@@ -148,6 +148,8 @@ def load():
     lib.vs_bank_set_depth.argtypes = [vp, i32, pf64, i32, i32]
     lib.vs_bank_get_corresponding.argtypes = [vp, i32, i32, i32, i32, pf64, pi32]
     lib.vs_bank_export.argtypes = [vp, i32, i32, pi32, pi32, pi32, pf64, pi32, pf64, pi32]
+    lib.vs_bank_debug_guard_check.argtypes = [vp]
+    lib.vs_bank_debug_guard_check.restype = i64
     _lib = lib
     return lib
 

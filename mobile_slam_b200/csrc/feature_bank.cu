@@ -15,6 +15,7 @@
 // iteration per feature here — depths agree to rounding (tests: 1e-9 relative), not bit for bit.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -482,6 +483,10 @@ int vs_bank_create(int32_t device, int32_t n_streams, int32_t capacity, vs_bank*
     b->device = device;
     b->d.B = n_streams;
     b->d.cap = capacity;
+    {   // VS_DEBUG_GUARD=1: every device block sits between two bands of 0xA5 that nothing may write (vs_bank_debug_guard_check)
+        const char* g = getenv("VS_DEBUG_GUARD");
+        b->arena.guarded = g && atoi(g) != 0;
+    }
     const size_t B = n_streams, C = capacity;
     auto fail = [&](cudaError_t e) { set_error("bank allocation: %s", cudaGetErrorString(e)); vs_bank_destroy(b); return VS_ERR_NOMEM; };
     cudaError_t e;
@@ -515,6 +520,14 @@ void vs_bank_destroy(vs_bank* b) {
     if (b->ev) cudaEventDestroy(b->ev);
     if (b->stream) cudaStreamDestroy(b->stream);
     delete b;
+}
+
+// bytes of the guard bands around the bank's device blocks that changed (-1: handle not created with VS_DEBUG_GUARD=1)
+int64_t vs_bank_debug_guard_check(vs_bank* b) {
+    if (!b) return -2;
+    cudaSetDevice(b->device);
+    cudaStreamSynchronize(b->stream);
+    return b->arena.check();
 }
 
 // clearState (fm:11-13) for one stream or all (-1)

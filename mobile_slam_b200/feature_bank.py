@@ -51,6 +51,10 @@ class FeatureBank:
 
     __del__ = close
 
+    def guard_check(self) -> int:
+        """Guard bytes overwritten so far (needs VS_DEBUG_GUARD=1 at creation; -1 otherwise)."""
+        return int(self._lib.vs_bank_debug_guard_check(self._h))
+
     def clear_state(self, stream: int = -1):
         _abi.check(self._lib.vs_bank_clear(self._h, stream))
 

@@ -203,3 +203,55 @@ def test_bank_errors(built_lib):
     with pytest.raises(VsError, match="out of range"):
         bank.export(2)
     bank.close()
+
+
+def _guard_child():
+    """Runs in a child interpreter with VS_DEBUG_GUARD=1: every bank kernel on small and on overflowing inputs, then the
+    number of guard bytes that changed around the bank's device blocks."""
+    import sys
+    worst = 0
+    bank = FeatureBank(3, capacity=300)
+    for s, (seed, speed) in enumerate([(1, 0.06), (2, 0.004), (4, 0.15)]):
+        fm_scenario.drive(StreamFeatureManager(bank, s), seed, 40, speed=speed)
+    worst = max(worst, bank.guard_check())
+    bank.close()
+    bank = FeatureBank(2, capacity=8)                      # more features than slots: refused, nothing written past the end
+    img = {i: [0.01 * i, 0.0, 1.0, 0, 0, 0, 0] for i in range(40)}
+    for k in range(3):
+        try:
+            bank.add_frames(k, [img, img])
+        except VsError:
+            pass
+    worst = max(worst, bank.guard_check())
+    bank.close()
+    cfg = CONFIGS["C1"]
+    tc, cam = config_from_synth(cfg, ransac_mode=VS_RANSAC_OFF)
+    bt = BatchTracker(tc, cam, 2)
+    bank = FeatureBank(2, capacity=160)                    # fills up within the window: the overflow path with tracker input
+    st = [SynthStream(5 + s, cfg["width"], cfg["height"], motion=3.0) for s in range(2)]
+    for k in range(14):
+        bt.track([q.frame(k) for q in st], [0.05 * k] * 2)
+        try:
+            bank.add_frames_from_tracker(bt, min(k, WINDOW_SIZE))
+        except VsError:
+            pass
+    worst = max(worst, bank.guard_check())
+    bank.close(); bt.close()
+    sys.stdout.write(f"GUARD {worst}\n")
+
+
+def test_bank_kernels_store_inside_their_buffers(built_lib):
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (f"import sys; sys.path.insert(0, {root!r}); sys.path.insert(0, {os.path.join(root, 'tests')!r}); "
+            "import test_gpu_feature_bank as T; T._guard_child()")
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, VS_DEBUG_GUARD="1"), capture_output=True, text=True,
+                       cwd=root, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("GUARD ")][-1]
+    assert int(line.split()[1]) == 0, f"{line}: guard bytes around the bank's device blocks were overwritten"
+    bank = FeatureBank(1, capacity=8)
+    assert bank.guard_check() == -1                        # created without guards: says so
+    bank.close()

@@ -274,7 +274,10 @@ VS_API void vs_ingest_destroy(struct vs_ingest* g);
  * [x, y, z, u, v, vx, vy] (common/image_frame.h:14, the layout vs_pack_image_features writes).  WINDOW_SIZE is 10
  * (utility/config.h:11): a feature holds at most VS_BANK_MAX_OBS observations.  Decisions, parallax sums and shifted
  * depths are bit-equal to the reference; triangulated depths agree to rounding (the SVD is a Jacobi iteration here,
- * Eigen::JacobiSVD there).  All calls synchronise the bank's own stream before returning. */
+ * Eigen::JacobiSVD there).  All calls synchronise the bank's own stream before returning; calls on one handle are
+ * serialised by the caller (like the reference's manager, which lives on the estimator's thread).  A stream whose bank
+ * overflowed (VS_ERR_CAPACITY from an add) holds an incomplete frame: every later add on the handle reports it again
+ * until vs_bank_clear resets that stream. */
 #define VS_BANK_WINDOW_SIZE 10
 #define VS_BANK_MAX_OBS (VS_BANK_WINDOW_SIZE + 1)
 struct vs_bank;

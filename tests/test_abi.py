@@ -82,6 +82,22 @@ def test_no_cpu_fallback_without_gpu(built_lib):
     assert "no CPU fallback" in str(e.value) or "CUDA" in str(e.value)
 
 
+def test_feature_bank_validates_arguments_and_has_no_cpu_path(built_lib):
+    import torch
+    h = C.c_void_p()
+    assert built_lib.vs_bank_create(0, 0, 16, C.byref(h)) == -1 and not h          # VS_ERR_INVALID before any CUDA call
+    assert built_lib.vs_bank_create(0, 1, 0, C.byref(h)) == -1 and not h
+    assert built_lib.vs_bank_create(0, 1, 16, None) == -1
+    assert built_lib.vs_bank_clear(None, 0) == -1 and b"null bank" in built_lib.vs_last_error()
+    assert built_lib.vs_bank_debug_guard_check(None) == -2
+    if not torch.cuda.is_available():
+        assert built_lib.vs_bank_create(0, 1, 16, C.byref(h)) == -2 and not h      # VS_ERR_CUDA: no device, no fallback
+        assert b"no CPU fallback" in built_lib.vs_last_error()
+        from mobile_slam_b200 import FeatureBank, VsError
+        with pytest.raises(VsError):
+            FeatureBank(1)
+
+
 def test_product_package_never_imports_oracle():
     # the product path must not route through oracle/: check statically and in a clean interpreter
     pkg = os.path.join(ROOT, "mobile_slam_b200")

@@ -45,4 +45,30 @@ for k in range(60):                                        # create / destroy
 free3 = torch.cuda.mem_get_info()[0]
 print(f"after 60 create/track/destroy cycles: {(free0 - free3) / 2**20:.1f} MiB not returned")
 assert free0 - free3 < 64 * 2**20
+# feature bank: a long estimator loop fed from the tracker on the device (window slides every frame), then create / destroy
+from mobile_slam_b200.feature_bank import OP_NONE, OP_REMOVE_BACK, OP_REMOVE_FRONT, WINDOW_SIZE, FeatureBank
+bt = BatchTracker(tc, cam, S)
+bank = FeatureBank(S, capacity=1024)
+free4 = torch.cuda.mem_get_info()[0]
+fcs = np.zeros(S, np.int32)
+sizes, n_bank = [], min(n_batches, 1500)
+for i in range(n_bank):
+    bt.track_pinned(pinned[idx(i)].data_ptr(), H * W, (C.c_double * S)(*([0.05 * i] * S)))
+    keys = bank.add_frames_from_tracker(bt, fcs)
+    full = fcs >= WINDOW_SIZE
+    bank.slide(np.where(full, np.where(keys, OP_REMOVE_BACK, OP_REMOVE_FRONT), OP_NONE).astype(np.int32), fcs)
+    fcs = np.where(full, fcs, fcs + 1).astype(np.int32)
+    if i % 250 == 249:
+        sizes.append(int(np.mean([len(bank.export(s_)[0]) for s_ in range(0, S, 4)])))
+free5 = torch.cuda.mem_get_info()[0]
+print(f"feature bank: {n_bank} frames x {S} streams, features per bank {min(sizes)}..{max(sizes)}, growth {(free4 - free5) / 2**20:.1f} MiB")
+assert max(sizes) < 1024 and min(sizes) > 60 and abs(free4 - free5) < 8 * 2**20
+bank.close(); bt.close()
+for k in range(60):
+    b3 = FeatureBank(8, capacity=512)
+    b3.add_frames(0, [{i: [0.01 * i, 0.0, 1.0, 0, 0, 0, 0] for i in range(50)}] * 8)
+    b3.close()
+free6 = torch.cuda.mem_get_info()[0]
+print(f"after 60 bank create/add/destroy cycles: {(free0 - free6) / 2**20:.1f} MiB not returned")
+assert free0 - free6 < 64 * 2**20
 print("soak ok")

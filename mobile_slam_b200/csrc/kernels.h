@@ -65,6 +65,7 @@ struct StParams {
     int W, H;
     int nx, ny, words_per_strip, rows_per_strip;   // strip grid (filled by launch_shi_tomasi)
     int skip_masked_rows;     // walk only the row steps that can reach an unmasked pixel (filled by launch_shi_tomasi)
+    int img_padded;           // img is a pyramid level stored with its REFLECT_101 border (>= 8 columns each side): frame path
     const int* want;          // [n_streams] corners wanted; streams with want <= 0 are skipped (may be null)
     // analytic mask = base minus the min_dist discs of the kept features
     const int* kn;            // [n_streams] kept features (may be null = none)

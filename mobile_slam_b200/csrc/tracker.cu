@@ -692,6 +692,7 @@ static int run_frame(vs_tracker* t, const uint8_t* d_img, int pitch, int64_t str
     launch_set_mask(g, t->stream, &t->launches, fuse_glue, fuse_ransac, ransac_seed(t));
     prof_tick(t, PK_SET_MASK);
     StParams e = make_st_params(t, nb, g);
+    e.img_padded = kPyrFirstPaddedLevel == 0 && kPyrPadX >= 8;       // build_pyramid wrote level 0's border columns
     launch_shi_tomasi(e, t->B, t->stream, &t->launches);
     prof_tick(t, PK_SHI_TOMASI);
     launch_select_finish(g, t->stream, &t->launches);

@@ -255,3 +255,20 @@ def test_bank_kernels_store_inside_their_buffers(built_lib):
     bank = FeatureBank(1, capacity=8)
     assert bank.guard_check() == -1                        # created without guards: says so
     bank.close()
+
+
+def test_erased_feature_returns_at_the_back_of_the_list(built_lib):
+    """removeFailures erases a feature the tracker still publishes: its id comes back as a NEW entry at the back, so the list
+    is no longer ordered by id — the device bank must keep the reference's list order (pinned against the compiled reference
+    in tests/test_oracle_feature_manager.py)."""
+    from test_oracle_feature_manager import _apply_reuse, _reuse_ops
+    bank = FeatureBank(2, capacity=64)
+    dev, ora = StreamFeatureManager(bank, 1), FeatureManager()
+    for k, op in enumerate(_reuse_ops()):
+        r1, r2 = _apply_reuse(ora, op), _apply_reuse(dev, op)
+        assert r1 == r2, (k, op[0])
+        _same_state(dev, ora, f"reuse op {k} {op[0]}")
+    ids = list(dev.export()[0])
+    assert ids != sorted(ids) and ids.index(5) > ids.index(30)
+    assert len(bank.export(0)[0]) == 0
+    bank.close()

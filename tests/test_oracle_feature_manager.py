@@ -93,3 +93,40 @@ def test_clear_state():
         m.add_feature_and_check_parallax(0, img)
     _same_state(py, ref, "after clear")
     assert len(py.bank) == 2
+
+
+def _reuse_ops():
+    """A feature erased by removeFailures while the tracker still publishes its id comes back as a NEW list entry at the
+    back (the list is then no longer ordered by id); an empty frame and a single-feature frame ride along."""
+    def img(ids, k):
+        return {i: [0.01 * i + 0.002 * k, -0.005 * i, 1.0, 100.0 + i, 50.0 + k, 0.1, -0.1] for i in ids}
+    ops = [("add", 0, img(range(1, 31), 0)), ("add", 1, img(range(1, 31), 1)), ("add", 2, img(range(1, 31), 2))]
+    ops.append(("set_depth_by_id", {5: -2.0, 17: -0.5}))       # inverse depths: negative => solve_flag 2
+    ops.append(("remove_failures",))
+    ops.append(("add", 3, img(list(range(1, 31)) + [40, 33], 3)))    # 5 and 17 return, 33 and 40 are new: order 5, 17, 33, 40
+    ops.append(("add", 4, {}))
+    ops.append(("add", 5, img([33], 5)))
+    ops.append(("remove_back",))      # (removeFront is only defined for frame_count == WINDOW_SIZE: estimator.cpp:311)
+    ops.append(("remove_back",))
+    return ops
+
+
+def _apply_reuse(fm, op):
+    if op[0] == "add":
+        return fm.add_feature_and_check_parallax(op[1], op[2])
+    if op[0] == "set_depth_by_id":
+        ids, start, n_obs, depth, flag, obs = fm.export()
+        x = [op[1].get(int(i), 0.25) for i, s, n in zip(ids, start, n_obs) if n >= 2 and s < WINDOW_SIZE - 2]
+        return fm.set_depth(x)
+    return getattr(fm, op[0])(*op[1:])
+
+
+def test_erased_feature_returns_at_the_back_of_the_list():
+    py = FeatureManager(); ref = ref_fm_binding.CompiledRefFeatureManager()
+    for k, op in enumerate(_reuse_ops()):
+        r1, r2 = _apply_reuse(py, op), _apply_reuse(ref, op)
+        assert r1 == r2, (k, op[0])
+        _same_state(py, ref, f"reuse op {k} {op[0]}")
+    ids = [it.feature_id for it in py.bank]
+    assert ids != sorted(ids) and ids.index(5) > ids.index(30) and ids.index(17) > ids.index(30)
+    assert ids.index(5) < ids.index(17) < ids.index(33) < ids.index(40)
